@@ -1,0 +1,190 @@
+#!/usr/bin/env python
+"""Headline benchmark: fused 2-D 5-point stencil, 16384 x 16384 fp64 cells per GPU.
+
+Metric (BASELINE.json): 2D-stencil Gcell-updates/s at 1/2/4/8 B200, device
+timed, max over ranks.  Weak scaling: every GPU owns a 16384^2 tile of a
+periodic Py x Px Cartesian grid (1x1, 1x2, 2x2, 2x4); one step = one Jacobi
+sweep of every tile INCLUDING the halo exchange, which is fused into the same
+kernel (peer stores over NVLink + device-side epoch flags).
+
+    python bench.py --gpus 1 --steps 20 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
+        --master-addr 127.0.0.1 --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 3
+
+Rank 0 prints ONE JSON line.  ``--impl reference`` is the reference arm: the
+reference cannot be installed or built on this image (no setup.py/pyproject,
+and no MPI library or compiler wrapper anywhere), so it reports
+``unavailable``; see DESIGN.md "Reference arm".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def parse_args(argv=None):
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--tile", type=int, default=16384, help="cells per side of each GPU's tile")
+    ap.add_argument("--radius", type=int, default=1)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    return ap.parse_args(argv)
+
+
+def reference_arm(args) -> int:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank == 0:
+        print(json.dumps({
+            "impl": "reference",
+            "unavailable": "reference is a set of C++/MPI main() programs with no setup.py/"
+                           "pyproject (pip: 'not installable') and this image has no MPI "
+                           "(mpicxx, mpi.h, libmpi, mpi4py all absent), so it cannot be built",
+        }))
+    return 0
+
+
+def main(argv=None) -> int:
+    args = parse_args(argv)
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import cuda_mpi_scratch_b200 as cms
+    from cuda_mpi_scratch_b200.models.stencil2d import Stencil2D, jacobi_coeffs
+    from cuda_mpi_scratch_b200.utils.timing import ClockSampler
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device"}))
+        return 1
+    world = cms.init()
+    n = world.size
+    if n != args.gpus:
+        if world.rank == 0:
+            print(f"warning: --gpus {args.gpus} but WORLD_SIZE={n}; using {n}", file=sys.stderr)
+    dims = cms.dims_create(n, 2)
+    if args.scaling == "weak":
+        th = tw = args.tile
+    else:  # strong: total work fixed at tile^2, split over the grid
+        th, tw = args.tile // dims[0], args.tile // dims[1]
+    R = args.radius
+    st = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True)
+    dev = st.device
+
+    # synthetic data: smooth deterministic field generated per tile on the device
+    # (state, like weights: it stays resident; per-step INPUTS are the coefficients)
+    r, c = st.cart.coords(world.rank)
+    ys = torch.arange(th, device=f"cuda:{dev}", dtype=torch.float64) + r * th
+    xs = torch.arange(tw, device=f"cuda:{dev}", dtype=torch.float64) + c * tw
+    st.fill(0.0, 0.0)
+    st.core.copy_(torch.sin(ys * 1e-3)[:, None] * torch.cos(xs * 2e-3)[None, :])
+    del ys, xs
+    coeffs = jacobi_coeffs(R)
+    st.set_coeffs(coeffs)
+    torch.cuda.synchronize(dev)
+    st.exchange()
+    torch.cuda.synchronize(dev)
+    world.barrier()
+
+    stream = torch.cuda.current_stream(dev)
+    # ---------------- device-timed: K fused steps ----------------
+    st.step(args.warmup)
+    torch.cuda.synchronize(dev)
+    world.barrier()
+    sampler = ClockSampler(dev).start() if world.rank == 0 else None
+    launches0 = st.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    world.barrier()
+    e0.record(stream)
+    st.step(args.steps)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    world.barrier()
+    ms = e0.elapsed_time(e1)
+    launches = st.kernel_launches - launches0
+    ms_max = world.allreduce_max(ms)
+    st.check()
+
+    # ---------------- end to end through the public API ----------------
+    # every step: H2D of that step's coefficients from pinned memory, one fused
+    # step with residual, D2H of the residual, host reads it.
+    coef_host = torch.tensor(coeffs, dtype=torch.float64).pin_memory()
+    h2d = coef_host.numel() * 8
+    d2h = 8
+    for _ in range(max(1, args.warmup)):
+        st.set_coeffs(coef_host)
+        st.step(1, residual=True)
+        st.local_residual_async()
+        stream.synchronize()
+    world.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    res = 0.0
+    for _ in range(args.steps):
+        st.set_coeffs(coef_host)
+        st.step(1, residual=True)
+        buf = st.local_residual_async()
+        stream.synchronize()
+        res = float(buf.item())
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    e2e_s = world.allreduce_max(e2e_s)
+    clocks = sampler.stop() if sampler is not None else None
+    st.check()
+
+    cells = float(th) * float(tw) * n
+    value = cells * args.steps / (ms_max * 1e-3) / 1e9
+    e2e_value = cells * args.steps / e2e_s / 1e9
+    if world.rank == 0:
+        bytes_per_cell = 16.0
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                                                "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm = peaks.get("hbm_gbs", 6650.0)
+        per_gpu = value / n
+        out = {
+            "metric": "2D-stencil Gcell-updates/s (5-point fp64, fused halo exchange)",
+            "value": round(value, 3), "unit": "Gcell/s", "n_gpus": n, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 5),
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+            "dtype": "fp64", "data": "synthetic",
+            "impl": "ours",
+            "config": {"model": f"stencil2d star radius {R} ({4 * R + 1}-point) Jacobi, periodic",
+                       "tile_per_gpu": [th, tw], "global_grid": [th * dims[0], tw * dims[1]],
+                       "process_grid": list(dims), "global_batch": int(cells), "seq_len": None,
+                       "parallelism": f"cart{dims[0]}x{dims[1]} 2-D domain decomposition",
+                       "l2": "inputs larger than L2 (2 x %.2f GiB per GPU vs 126 MB)"
+                             % (th * tw * 8 / 2 ** 30),
+                       "halo": "fused: peer stores + epoch flags inside the stencil kernel"},
+            "roofline": {"hbm_gbs_measured": hbm,
+                         "achieved_gbs_per_gpu": round(per_gpu * bytes_per_cell, 1),
+                         "fraction_of_measured_hbm": round(per_gpu * bytes_per_cell / hbm, 4)},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 3), "unit": "Gcell/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "what": "Stencil2D.set_coeffs(pinned) + step(1, residual=True) + residual "
+                            "D2H + host read, every step; wall clock, max over ranks",
+                    "last_residual_sumsq": res},
+            "gpu_launches": launches,
+            "launches_note": "per step: 1 fused stencil+halo kernel; +1 flag drain at the end",
+        }
+        print(json.dumps(out))
+    world.barrier()
+    st.close()
+    world.finalize()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

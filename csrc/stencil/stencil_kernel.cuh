@@ -1,0 +1,362 @@
+// Fused stencil update + halo exchange for one rank's tile (sm_100a).
+//
+// What the reference does per time step (stencil2d/mpi-2d-stencil-subarray-cuda.cu:169-172):
+//   ExchangeData()  -> 8 MPI_Irecv + 8 MPI_Isend of subarray types on a device
+//                      pointer + MPI_Waitall (stencil2d/stencil2D.h:363-377)
+//   Compute()       -> empty stub (:32-33)
+// i.e. host-driven, no overlap, and no stencil at all.
+//
+// What this kernel does per time step, in ONE launch per rank and with no host
+// or MPI involvement:
+//   * a persistent grid (<= 2 CTAs per SM) walks the tile list with the
+//     boundary ring FIRST;
+//   * one producer thread per CTA feeds a 3-stage shared-memory ring with 2-D
+//     TMA box loads (cp.async.bulk.tensor) completed on mbarriers;
+//   * 8 consumer warps apply the radius-R star (or 3x3 box) stencil from
+//     shared memory with a register sliding window and write 16-byte aligned
+//     rows of the output tile;
+//   * consumers of a boundary tile also store the freshly computed edge cells
+//     straight into the NEIGHBOUR GPU's ghost cells (peer addresses over
+//     NVLink), then one thread release-increments that neighbour's per-direction
+//     epoch counter (red.release.sys);
+//   * before a boundary tile is loaded, the producer acquires (ld.acquire.sys)
+//     the epoch counters of the directions whose ghost cells the tile reads --
+//     the device-side replacement of MPI_Waitall.  The same acquire also
+//     protects the write-after-read hazard on the neighbour's ghost cells of
+//     the double-buffered grid (see DESIGN.md "halo protocol").
+// Interior tiles never wait, so the halo traffic is in flight while ~98 % of
+// the tile list is being computed.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kernels/ptx.cuh"
+
+namespace b200 {
+namespace stencil {
+
+constexpr int kTileW = 128;        // output cells per tile row (1 KiB of fp64)
+constexpr int kTileH = 32;         // output rows per tile
+constexpr int kConsumers = 256;    // 8 consumer warps
+constexpr int kThreads = kConsumers + 32;  // + 1 producer warp
+constexpr int kRowsPerThread = 8;  // 4 row bands x 8 rows, 64 column pairs
+constexpr int kMaxRadius = 4;
+
+// Neighbour directions, numbered like the reference's MPIGridCellID
+// (stencil2d/stencil2D.h:86-88): NW N NE W E SW S SE.
+enum Dir : int { NW = 0, N = 1, NE = 2, W_ = 3, E_ = 4, SW = 5, S = 6, SE = 7 };
+__host__ __device__ constexpr int dir_dy(int d) { return d < 3 ? -1 : (d < 5 ? 0 : 1); }
+__host__ __device__ constexpr int dir_dx(int d) {
+    return (d == 0 || d == 3 || d == 5) ? -1 : ((d == 1 || d == 6) ? 0 : 1);
+}
+__host__ __device__ constexpr int dir_opposite(int d) { return 7 - d; }
+
+template <int R>
+struct Geo {
+    static constexpr int RA = (R + 1) & ~1;  // column halo rounded up to 16 B
+    static constexpr int BOXW = kTileW + 2 * RA;
+    static constexpr int BOXH = kTileH + 2 * R;
+    static constexpr int BOX_BYTES = BOXW * BOXH * 8;
+    static constexpr int STAGE_BYTES = (BOX_BYTES + 127) & ~127;
+};
+
+struct LaunchParams {
+    double* out;               // local padded output buffer
+    const double* in;          // local padded input buffer (same layout)
+    const double* coef;        // device coefficients (layout: see Stencil2D docs)
+    double* peer_out[8];       // neighbour's output buffer per direction (nullptr: none)
+    uint64_t* peer_flag[8];    // neighbour's epoch counter that I bump per direction
+    const uint64_t* my_flags;  // my 8 epoch counters (indexed by the direction data comes from)
+    uint64_t wait_epoch[8];    // value my_flags[d] must reach before ghost cells of d are read
+    double* resid_partials;    // [gridDim.x] per-CTA sum of (out-in)^2, or nullptr
+    unsigned int* status;      // device status word (bit0: flag wait timed out)
+    uint64_t timeout_ns;       // spin deadline per wait
+    int W, H;                  // core size in cells
+    int g;                     // ghost width (== stencil radius)
+    int lead;                  // column of the first core cell inside a padded row
+    int pitch;                 // elements per padded row
+    int tilesX, tilesY;
+    int push_corners;          // also exchange the 4 corner blocks
+};
+
+__device__ __forceinline__ void decode_tile(int i, int nbx, int nby, int& tx, int& ty) {
+    // Boundary ring first, then interior strips with y fastest.
+    if (nby == 1) { tx = i; ty = 0; return; }
+    if (i < nbx) { tx = i; ty = 0; return; }
+    i -= nbx;
+    if (i < nbx) { tx = i; ty = nby - 1; return; }
+    i -= nbx;
+    const int mid = nby - 2;
+    if (i < mid) { tx = 0; ty = 1 + i; return; }
+    i -= mid;
+    if (nbx > 1) {
+        if (i < mid) { tx = nbx - 1; ty = 1 + i; return; }
+        i -= mid;
+    }
+    tx = 1 + i / mid;
+    ty = 1 + i % mid;
+}
+
+// Bit d set <=> the tile touches the tile edge facing direction d.
+__device__ __forceinline__ unsigned edge_mask(int tx, int ty, int nbx, int nby) {
+    const bool n = ty == 0, s = ty == nby - 1, w = tx == 0, e = tx == nbx - 1;
+    unsigned m = 0;
+    if (n) m |= 1u << N;
+    if (s) m |= 1u << S;
+    if (w) m |= 1u << W_;
+    if (e) m |= 1u << E_;
+    if (n && w) m |= 1u << NW;
+    if (n && e) m |= 1u << NE;
+    if (s && w) m |= 1u << SW;
+    if (s && e) m |= 1u << SE;
+    return m;
+}
+
+__device__ __forceinline__ unsigned active_dirs(const LaunchParams& P, unsigned m) {
+    unsigned a = 0;
+#pragma unroll
+    for (int d = 0; d < 8; ++d) {
+        const bool corner = (d == NW || d == NE || d == SW || d == SE);
+        if ((m >> d & 1u) && P.peer_out[d] != nullptr && (!corner || P.push_corners)) a |= 1u << d;
+    }
+    return a;
+}
+
+template <int R, bool BOX, bool RESID, int NSTAGES>
+__global__ void __launch_bounds__(kThreads, (NSTAGES <= 3 && R <= 2) ? 2 : 1)
+stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
+                     const __grid_constant__ LaunchParams P) {
+    using G = Geo<R>;
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + NSTAGES * G::STAGE_BYTES);
+    uint64_t* empty = full + NSTAGES;
+    __shared__ double red_smem[kConsumers / 32];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int nbx = P.tilesX, nby = P.tilesY;
+    const int ntiles = nbx * nby;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < NSTAGES; ++s) {
+            ptx::mbar_init(&full[s], 1);
+            ptx::mbar_init(&empty[s], kConsumers / 32);
+        }
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp == kConsumers / 32) {
+        // ===================== producer: flag acquire + TMA =====================
+        if (lane == 0) {
+            ptx::prefetch_tensormap(&tmap_in);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int i = blockIdx.x; i < ntiles; i += gridDim.x) {
+                int tx, ty;
+                decode_tile(i, nbx, nby, tx, ty);
+                const unsigned act = active_dirs(P, edge_mask(tx, ty, nbx, nby));
+                if (act) {
+                    const uint64_t t0 = ptx::globaltimer_ns();
+                    for (int d = 0; d < 8; ++d) {
+                        if (!(act >> d & 1u)) continue;
+                        uint32_t spins = 0;
+                        while (ptx::ld_acquire_sys(P.my_flags + d) < P.wait_epoch[d]) {
+                            if ((++spins & 1023u) == 0 &&
+                                ptx::globaltimer_ns() - t0 > P.timeout_ns) {
+                                atomicOr(P.status, 1u);
+                                break;
+                            }
+                        }
+                    }
+                    // ghost cells were written by another GPU's generic proxy;
+                    // the TMA below reads them through the async proxy.
+                    ptx::fence_proxy_async();
+                }
+                ptx::mbar_wait(&empty[stage], phase ^ 1u);
+                ptx::mbar_arrive_expect_tx(&full[stage], G::BOX_BYTES);
+                ptx::tma_load_2d(smem + stage * G::STAGE_BYTES, &tmap_in,
+                                 P.lead + tx * kTileW - G::RA, ty * kTileH + P.g - R, &full[stage]);
+                if (++stage == NSTAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+        return;
+    }
+
+    // =============================== consumers ===============================
+    constexpr int NCOEF = BOX ? (2 * R + 1) * (2 * R + 1) : 4 * R + 1;
+    double c[NCOEF];
+#pragma unroll
+    for (int k = 0; k < NCOEF; ++k) c[k] = __ldg(P.coef + k);
+
+    const int cpair = tid & 63;       // column pair inside the tile
+    const int band = tid >> 6;        // row band (4 bands of kRowsPerThread rows)
+    const int c0 = 2 * cpair;         // first of my two columns (tile coords)
+    const int r0 = band * kRowsPerThread;
+    double racc = 0.0;
+
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = blockIdx.x; i < ntiles; i += gridDim.x) {
+        int tx, ty;
+        decode_tile(i, nbx, nby, tx, ty);
+        const unsigned act = active_dirs(P, edge_mask(tx, ty, nbx, nby));
+
+        ptx::mbar_wait(&full[stage], phase);
+        const double* box = reinterpret_cast<const double*>(smem + stage * G::STAGE_BYTES);
+        // box(row, col): row = tile row + R, col = tile col + RA
+        const double* mycol = box + c0 + G::RA;
+
+        double2 res[kRowsPerThread];
+        if constexpr (!BOX) {
+            double2 win[2 * R + 1];
+#pragma unroll
+            for (int k = 0; k < 2 * R; ++k)
+                win[k] = *reinterpret_cast<const double2*>(mycol + (r0 + k) * G::BOXW);
+#pragma unroll
+            for (int y = 0; y < kRowsPerThread; ++y) {
+                win[2 * R] =
+                    *reinterpret_cast<const double2*>(mycol + (r0 + y + 2 * R) * G::BOXW);
+                // horizontal strip of the centre row: cols c0-RA .. c0+1+RA
+                double h[2 * G::RA + 2];
+                const double* crow = mycol + (r0 + y + R) * G::BOXW - G::RA;
+#pragma unroll
+                for (int k = 0; k < G::RA + 1; ++k) {
+                    if (2 * k == G::RA) {
+                        h[2 * k] = win[R].x;
+                        h[2 * k + 1] = win[R].y;
+                    } else {
+                        const double2 v = *reinterpret_cast<const double2*>(crow + 2 * k);
+                        h[2 * k] = v.x;
+                        h[2 * k + 1] = v.y;
+                    }
+                }
+                double ax = c[0] * win[R].x, ay = c[0] * win[R].y;
+#pragma unroll
+                for (int k = 1; k <= R; ++k) {
+                    const int b = 1 + 4 * (k - 1);
+                    ax = fma(c[b + 0], h[G::RA - k], ax);       // west
+                    ay = fma(c[b + 0], h[G::RA + 1 - k], ay);
+                    ax = fma(c[b + 1], h[G::RA + k], ax);       // east
+                    ay = fma(c[b + 1], h[G::RA + 1 + k], ay);
+                    ax = fma(c[b + 2], win[R - k].x, ax);       // north
+                    ay = fma(c[b + 2], win[R - k].y, ay);
+                    ax = fma(c[b + 3], win[R + k].x, ax);       // south
+                    ay = fma(c[b + 3], win[R + k].y, ay);
+                }
+                res[y] = make_double2(ax, ay);
+                if constexpr (RESID) {
+                    const int gy = ty * kTileH + r0 + y, gx = tx * kTileW + c0;
+                    if (gy < P.H && gx < P.W) {
+                        const double dx_ = ax - win[R].x, dy_ = ay - win[R].y;
+                        racc = fma(dx_, dx_, racc);
+                        racc = fma(dy_, dy_, racc);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 2 * R; ++k) win[k] = win[k + 1];
+            }
+        } else {
+#pragma unroll
+            for (int y = 0; y < kRowsPerThread; ++y) {
+                double ax = 0.0, ay = 0.0, cx = 0.0, cy = 0.0;
+#pragma unroll
+                for (int dy = -R; dy <= R; ++dy) {
+                    double h[2 * G::RA + 2];
+                    const double* crow = mycol + (r0 + y + R + dy) * G::BOXW - G::RA;
+#pragma unroll
+                    for (int k = 0; k < G::RA + 1; ++k) {
+                        const double2 v = *reinterpret_cast<const double2*>(crow + 2 * k);
+                        h[2 * k] = v.x;
+                        h[2 * k + 1] = v.y;
+                    }
+                    if (dy == 0) { cx = h[G::RA]; cy = h[G::RA + 1]; }
+#pragma unroll
+                    for (int dx = -R; dx <= R; ++dx) {
+                        const double w = c[(dy + R) * (2 * R + 1) + (dx + R)];
+                        ax = fma(w, h[G::RA + dx], ax);
+                        ay = fma(w, h[G::RA + 1 + dx], ay);
+                    }
+                }
+                res[y] = make_double2(ax, ay);
+                if constexpr (RESID) {
+                    const int gy = ty * kTileH + r0 + y, gx = tx * kTileW + c0;
+                    if (gy < P.H && gx < P.W) {
+                        racc = fma(ax - cx, ax - cx, racc);
+                        racc = fma(ay - cy, ay - cy, racc);
+                    }
+                }
+            }
+        }
+        // all shared-memory reads of this stage are done: hand it back to TMA
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&empty[stage]);
+
+        // ------------------------------ stores ------------------------------
+        const int gx = tx * kTileW + c0;  // core coords of my first column
+        if (gx < P.W) {
+#pragma unroll
+            for (int y = 0; y < kRowsPerThread; ++y) {
+                const int gy = ty * kTileH + r0 + y;
+                if (gy < P.H) {
+                    double* dst = P.out + (size_t)(gy + P.g) * P.pitch + P.lead + gx;
+                    *reinterpret_cast<double2*>(dst) = res[y];
+                }
+            }
+        }
+        if (act) {
+            // -------- halo push: edge cells go straight to the neighbours --------
+            if (gx < P.W) {
+#pragma unroll 1
+                for (int d = 0; d < 8; ++d) {
+                    if (!(act >> d & 1u)) continue;
+                    const int dy = dir_dy(d), dx = dir_dx(d);
+                    double* pb = P.peer_out[d];
+#pragma unroll
+                    for (int y = 0; y < kRowsPerThread; ++y) {
+                        const int gy = ty * kTileH + r0 + y;
+                        if (gy >= P.H) continue;
+                        const bool rowok = dy < 0 ? gy < P.g : (dy > 0 ? gy >= P.H - P.g : true);
+                        if (!rowok) continue;
+                        double* prow = pb + (size_t)(gy + P.g - dy * P.H) * P.pitch + P.lead -
+                                       dx * P.W;
+                        if (dx == 0) {
+                            *reinterpret_cast<double2*>(prow + gx) = res[y];
+                        } else {
+                            const bool ok0 = dx < 0 ? gx < P.g : gx >= P.W - P.g;
+                            const bool ok1 = dx < 0 ? gx + 1 < P.g : gx + 1 >= P.W - P.g;
+                            if (ok0) prow[gx] = res[y].x;
+                            if (ok1) prow[gx + 1] = res[y].y;
+                        }
+                    }
+                }
+            }
+            // every consumer's peer stores happen-before thread 0's release
+            ptx::named_bar_sync(1, kConsumers);
+            if (tid == 0) {
+                for (int d = 0; d < 8; ++d)
+                    if (act >> d & 1u) ptx::red_add_release_sys(P.peer_flag[d], 1ull);
+            }
+        }
+        if (++stage == NSTAGES) { stage = 0; phase ^= 1u; }
+    }
+
+    if constexpr (RESID) {
+        // deterministic per-CTA partial: lanes -> warps -> thread 0
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) racc += __shfl_xor_sync(0xffffffffu, racc, o);
+        if (lane == 0) red_smem[warp] = racc;
+        ptx::named_bar_sync(2, kConsumers);
+        if (tid == 0) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < kConsumers / 32; ++w) s += red_smem[w];
+            P.resid_partials[blockIdx.x] = s;
+        }
+    }
+}
+
+}  // namespace stencil
+}  // namespace b200

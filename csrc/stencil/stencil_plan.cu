@@ -1,0 +1,462 @@
+// Host side of the fused stencil: per-rank plan, layout, tensor maps, launches,
+// plus the small unfused halo kernels (initial exchange, drain).
+//
+// Reference counterpart (capability only): the driver program
+// stencil2d/mpi-2d-stencil-subarray-cuda.cu:126-172 (allocate tile + ghosts,
+// build 16 TransferInfo, loop ExchangeData/Compute/TerminateCondition) and the
+// plan builder stencil2d/stencil2D.h:381-437.  Here the "plan" is a table of 8
+// peer base pointers + 8 epoch counters living in a symmetric allocation, and
+// the loop body is one kernel.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "b200comm.h"
+#include "b200comm/error.hpp"
+#include "core/capi_util.hpp"
+#include "stencil/stencil_kernel.cuh"
+
+namespace b200 {
+namespace stencil {
+
+// ---- control pad layout (first kPadBytes of every rank's symmetric block) ----
+constexpr size_t kPadBytes = 4096;
+constexpr size_t kOffStepFlags = 0;     // 8 x u64: fused-step epoch counters
+constexpr size_t kOffXchgFlags = 64;    // 8 x u64: unfused-exchange epoch counters
+constexpr size_t kOffStatus = 128;      // u32 status word
+constexpr size_t kOffResid = 256;       // double: last local residual (sum of squares)
+constexpr size_t kOffRedSlots = 1024;   // scalar allreduce slots (see collectives)
+
+constexpr int kLead = 16;  // core starts 128 B into each padded row
+
+struct Layout {
+    int W, H, R, g, lead, pitch, rows;
+    size_t tile_bytes;   // one padded buffer
+    size_t off_x[2];     // offsets of the two buffers inside the symmetric block
+    size_t total_bytes;
+};
+
+static Layout make_layout(int W, int H, int R) {
+    Layout L{};
+    L.W = W; L.H = H; L.R = R; L.g = R; L.lead = kLead;
+    const int RA = (R + 1) & ~1;
+    const int need = kLead + W + (R > RA ? R : RA);
+    L.pitch = (need + 15) & ~15;
+    L.rows = H + 2 * R;
+    L.tile_bytes = ((size_t)L.pitch * L.rows * sizeof(double) + 1023) & ~(size_t)1023;
+    L.off_x[0] = kPadBytes;
+    L.off_x[1] = kPadBytes + L.tile_bytes;
+    L.total_bytes = kPadBytes + 2 * L.tile_bytes;
+    return L;
+}
+
+// ------------------------------ small kernels ------------------------------
+
+struct XchgParams {
+    const double* src;        // my current buffer
+    double* peer[8];          // neighbours' current buffers
+    uint64_t* peer_flag[8];   // neighbours' xchg counters (slot opposite(d))
+    int W, H, g, lead, pitch;
+};
+
+// Unfused halo push of the current buffer: region d of my core -> ghost region
+// opposite(d) of neighbour d.  One CTA per direction, so the CTA itself is the
+// last writer and can publish.  Edges are at most W*g or H*g elements (128 KiB
+// for 16384 x 1): a set-up path, not worth a grid-wide arrival counter.
+__global__ void halo_push1_kernel(const __grid_constant__ XchgParams P) {
+    const int d = blockIdx.x;
+    double* pb = P.peer[d];
+    if (pb == nullptr) return;
+    const int dy = dir_dy(d), dx = dir_dx(d);
+    const int rows = dy == 0 ? P.H : P.g, cols = dx == 0 ? P.W : P.g;
+    const int y0 = dy > 0 ? P.H - P.g : 0, x0 = dx > 0 ? P.W - P.g : 0;
+    const long n = (long)rows * cols;
+    for (long i = threadIdx.x; i < n; i += blockDim.x) {
+        const int y = y0 + (int)(i / cols), x = x0 + (int)(i % cols);
+        const double v = P.src[(size_t)(y + P.g) * P.pitch + P.lead + x];
+        pb[(size_t)(y + P.g - dy * P.H) * P.pitch + P.lead + x - dx * P.W] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) ptx::red_add_release_sys(P.peer_flag[d], 1ull);
+}
+
+struct WaitParams {
+    const uint64_t* flags;   // 8 counters
+    uint64_t epoch[8];       // required values (0: do not wait)
+    unsigned int* status;
+    uint64_t timeout_ns;
+};
+
+// Device-side replacement of MPI_Waitall (stencil2d/stencil2D.h:375-376): one
+// thread per direction acquires its counter.
+__global__ void flag_wait_kernel(const __grid_constant__ WaitParams P) {
+    const int d = threadIdx.x;
+    if (d >= 8 || P.epoch[d] == 0) return;
+    const uint64_t t0 = ptx::globaltimer_ns();
+    uint32_t spins = 0;
+    while (ptx::ld_acquire_sys(P.flags + d) < P.epoch[d]) {
+        if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
+            atomicOr(P.status, 1u);
+            break;
+        }
+    }
+}
+
+__global__ void sum_partials_kernel(const double* __restrict__ partials, int n, double* out) {
+    __shared__ double sh[256];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += partials[i];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = sh[0];
+}
+
+// Fill a rectangle of a padded tile (tiled launch; the reference's InitKernel
+// uses one thread per block, stencil2d/mpi-2d-stencil-subarray-cuda.cu:17-28).
+__global__ void fill_rect_kernel(double* base, int pitch, int x0, int y0, int w, int h, double v) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x < w && y < h) base[(size_t)(y0 + y) * pitch + x0 + x] = v;
+}
+
+// ------------------------------ plan ------------------------------
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    B200_CHECK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    B200_REQUIRE(p != nullptr && q == cudaDriverEntryPointSuccess, ERR_CUDA,
+                 "cuTensorMapEncodeTiled not available from the driver");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+    return fn;
+}
+
+struct Plan {
+    Layout L;
+    int kind;          // 0 star, 1 box
+    int push_corners;
+    int device;
+    unsigned char* base;         // my symmetric block
+    unsigned char* nbr[8];       // neighbours' symmetric blocks (peer mapped) or nullptr
+    CUtensorMap tmap[2];
+    double* coef_dev;
+    int ncoef;
+    double* resid_partials;
+    uint64_t steps_done;         // fused steps completed since creation
+    uint64_t xchg_done;          // unfused exchanges completed
+    int cur;                     // index of the buffer holding the current state
+    int grid, nstages, ctas_per_sm;
+    size_t smem;
+    uint64_t timeout_ns;
+    int tilesX, tilesY;
+};
+
+template <int R, bool BOX, bool RESID, int NST>
+static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) {
+    auto k = stencil_fused_kernel<R, BOX, RESID, NST>;
+    static bool attr_done[64] = {};
+    if (!attr_done[pl.device & 63]) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)pl.smem));
+        attr_done[pl.device & 63] = true;
+    }
+    k<<<pl.grid, kThreads, pl.smem, st>>>(pl.tmap[pl.cur], lp);
+    B200_CHECK_LAUNCH();
+}
+
+template <int R, bool BOX>
+static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    constexpr int NST = R <= 2 ? 3 : 4;
+    if (resid) launch_one<R, BOX, true, NST>(pl, lp, st);
+    else launch_one<R, BOX, false, NST>(pl, lp, st);
+}
+
+static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.kind == 0) {
+        switch (pl.L.R) {
+            case 1: launch_r<1, false>(pl, lp, resid, st); return;
+            case 2: launch_r<2, false>(pl, lp, resid, st); return;
+            case 3: launch_r<3, false>(pl, lp, resid, st); return;
+            case 4: launch_r<4, false>(pl, lp, resid, st); return;
+        }
+    } else {
+        switch (pl.L.R) {
+            case 1: launch_r<1, true>(pl, lp, resid, st); return;
+            case 2: launch_r<2, true>(pl, lp, resid, st); return;
+        }
+    }
+    B200_FAIL(ERR_ARG, "unsupported stencil kind/radius");
+}
+
+static uint64_t contributions(const Plan& pl, int d) {
+    const int dy = dir_dy(d), dx = dir_dx(d);
+    if (dy != 0 && dx != 0) return 1;
+    return dy != 0 ? (uint64_t)pl.tilesX : (uint64_t)pl.tilesY;
+}
+
+static bool dir_active(const Plan& pl, int d) {
+    const bool corner = dir_dy(d) != 0 && dir_dx(d) != 0;
+    return pl.nbr[d] != nullptr && (!corner || pl.push_corners);
+}
+
+}  // namespace stencil
+}  // namespace b200
+
+using namespace b200;
+using namespace b200::stencil;
+
+struct b2c_stencil { Plan p; };
+
+extern "C" {
+
+B2C_EXPORT int b2c_stencil_layout(int W, int H, int R, b2c_stencil_layout_t* out) {
+    B2C_TRY
+    B200_REQUIRE(out != nullptr, ERR_ARG, "null output");
+    B200_REQUIRE(W >= 2 && H >= 1 && (W % 2) == 0, ERR_ARG, "tile width must be even and >= 2");
+    B200_REQUIRE(R >= 1 && R <= kMaxRadius, ERR_ARG, "radius must be in [1,4]");
+    B200_REQUIRE(W >= R && H >= R, ERR_ARG, "tile smaller than the stencil radius");
+    Layout L = make_layout(W, H, R);
+    out->W = W; out->H = H; out->radius = R; out->ghost = L.g; out->lead = L.lead;
+    out->pitch = L.pitch; out->rows = L.rows; out->tile_bytes = L.tile_bytes;
+    out->off_buf0 = L.off_x[0]; out->off_buf1 = L.off_x[1]; out->total_bytes = L.total_bytes;
+    out->pad_bytes = kPadBytes; out->off_red_slots = kOffRedSlots;
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int kind,
+                                  void* local_base, void* const nbr_base[8], int push_corners) {
+    B2C_TRY
+    B200_REQUIRE(out && local_base, ERR_ARG, "null argument");
+    B200_REQUIRE(kind == 0 || (kind == 1 && R <= 2), ERR_ARG,
+                 "kind must be 0 (star, R<=4) or 1 (box, R<=2)");
+    b2c_stencil_layout_t tmp;
+    int rc = b2c_stencil_layout(W, H, R, &tmp);
+    if (rc) return rc;
+    auto* h = new (std::nothrow) b2c_stencil();
+    B200_REQUIRE(h, ERR_NOMEM, "plan allocation failed");
+    Plan& p = h->p;
+    std::memset(&p, 0, sizeof(p));
+    p.L = make_layout(W, H, R);
+    p.kind = kind;
+    p.push_corners = (kind == 1) ? 1 : (push_corners != 0);
+    B200_CHECK_CUDA(cudaGetDevice(&p.device));
+    p.base = static_cast<unsigned char*>(local_base);
+    for (int d = 0; d < 8; ++d) p.nbr[d] = static_cast<unsigned char*>(nbr_base ? nbr_base[d] : nullptr);
+    p.tilesX = (W + kTileW - 1) / kTileW;
+    p.tilesY = (H + kTileH - 1) / kTileH;
+    p.timeout_ns = 20ull * 1000 * 1000 * 1000;
+
+    // shared memory / grid
+    const int RA = (R + 1) & ~1;
+    const size_t stage = (((size_t)(kTileW + 2 * RA) * (kTileH + 2 * R) * 8) + 127) & ~(size_t)127;
+    p.nstages = R <= 2 ? 3 : 4;
+    p.ctas_per_sm = R <= 2 ? 2 : 1;
+    p.smem = p.nstages * stage + 2 * p.nstages * sizeof(uint64_t);
+    cudaDeviceProp prop;
+    B200_CHECK_CUDA(cudaGetDeviceProperties(&prop, p.device));
+    const int ntiles = p.tilesX * p.tilesY;
+    p.grid = prop.multiProcessorCount * p.ctas_per_sm;
+    if (p.grid > ntiles) p.grid = ntiles;
+
+    // tensor maps over the two padded buffers
+    EncodeTiledFn enc = get_encode_tiled();
+    for (int b = 0; b < 2; ++b) {
+        cuuint64_t gdim[2] = {(cuuint64_t)p.L.pitch, (cuuint64_t)p.L.rows};
+        cuuint64_t gstr[1] = {(cuuint64_t)p.L.pitch * sizeof(double)};
+        cuuint32_t box[2] = {(cuuint32_t)(kTileW + 2 * RA), (cuuint32_t)(kTileH + 2 * R)};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = enc(&p.tmap[b], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, p.base + p.L.off_x[b], gdim,
+                         gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        B200_REQUIRE(r == CUDA_SUCCESS, ERR_CUDA,
+                     "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    }
+    p.ncoef = kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1);
+    B200_CHECK_CUDA(cudaMalloc(&p.coef_dev, 128 * sizeof(double)));
+    B200_CHECK_CUDA(cudaMalloc(&p.resid_partials, (size_t)p.grid * sizeof(double)));
+    // default: Jacobi average of the 4R (or (2R+1)^2-1) neighbours
+    double hc[128] = {0};
+    const int nn = p.ncoef - 1;
+    if (kind == 0) { for (int k = 1; k < p.ncoef; ++k) hc[k] = 1.0 / nn; }
+    else { for (int k = 0; k < p.ncoef; ++k) hc[k] = (k == p.ncoef / 2) ? 0.0 : 1.0 / nn; }
+    B200_CHECK_CUDA(cudaMemcpy(p.coef_dev, hc, sizeof(double) * p.ncoef, cudaMemcpyHostToDevice));
+    *out = h;
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_destroy(b2c_stencil* h) {
+    B2C_TRY
+    if (!h) return 0;
+    cudaFree(h->p.coef_dev);
+    cudaFree(h->p.resid_partials);
+    delete h;
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_set_coef(b2c_stencil* h, const double* host_coef, int n, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h && host_coef, ERR_ARG, "null argument");
+    B200_REQUIRE(n == h->p.ncoef, ERR_COUNT,
+                 "coefficient count must be " + std::to_string(h->p.ncoef));
+    B200_CHECK_CUDA(cudaMemcpyAsync(h->p.coef_dev, host_coef, sizeof(double) * n,
+                                    cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_set_timeout_ms(b2c_stencil* h, unsigned long long ms) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    h->p.timeout_ns = ms * 1000000ull;
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_info(b2c_stencil* h, b2c_stencil_info_t* o) {
+    B2C_TRY
+    B200_REQUIRE(h && o, ERR_ARG, "null argument");
+    const Plan& p = h->p;
+    o->cur = p.cur; o->steps_done = p.steps_done; o->grid = p.grid; o->threads = kThreads;
+    o->smem_bytes = p.smem; o->nstages = p.nstages; o->tiles_x = p.tilesX; o->tiles_y = p.tilesY;
+    o->ncoef = p.ncoef; o->launches_per_step = 1;
+    o->buf[0] = p.base + p.L.off_x[0]; o->buf[1] = p.base + p.L.off_x[1];
+    o->resid = reinterpret_cast<double*>(p.base + kOffResid);
+    B2C_CATCH
+}
+
+static void drain_impl(Plan& p, bool xchg, cudaStream_t st) {
+    WaitParams wp{};
+    wp.flags = reinterpret_cast<const uint64_t*>(p.base + (xchg ? kOffXchgFlags : kOffStepFlags));
+    wp.status = reinterpret_cast<unsigned*>(p.base + kOffStatus);
+    wp.timeout_ns = p.timeout_ns;
+    bool any = false;
+    for (int d = 0; d < 8; ++d) {
+        wp.epoch[d] = 0;
+        if (!dir_active(p, d)) continue;
+        wp.epoch[d] = xchg ? p.xchg_done : p.steps_done * contributions(p, d);
+        any = any || wp.epoch[d] != 0;
+    }
+    if (!any) return;
+    flag_wait_kernel<<<1, 32, 0, st>>>(wp);
+    B200_CHECK_LAUNCH();
+}
+
+// Launch `nsteps` fused steps.  flags: bit0 = compute the residual of the LAST
+// step into the pad, bit1 = append the drain (wait until the neighbours' halo
+// pushes of the last step have landed, so ghosts of the current buffer are
+// complete when the stream is synchronised).
+B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h && nsteps >= 0, ERR_ARG, "bad argument");
+    Plan& p = h->p;
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int s = 0; s < nsteps; ++s) {
+        LaunchParams lp{};
+        const int in = p.cur, outb = p.cur ^ 1;
+        lp.in = reinterpret_cast<const double*>(p.base + p.L.off_x[in]);
+        lp.out = reinterpret_cast<double*>(p.base + p.L.off_x[outb]);
+        lp.coef = p.coef_dev;
+        lp.my_flags = reinterpret_cast<const uint64_t*>(p.base + kOffStepFlags);
+        lp.status = reinterpret_cast<unsigned*>(p.base + kOffStatus);
+        lp.timeout_ns = p.timeout_ns;
+        lp.resid_partials = p.resid_partials;
+        for (int d = 0; d < 8; ++d) {
+            if (dir_active(p, d)) {
+                lp.peer_out[d] = reinterpret_cast<double*>(p.nbr[d] + p.L.off_x[outb]);
+                lp.peer_flag[d] =
+                    reinterpret_cast<uint64_t*>(p.nbr[d] + kOffStepFlags) + dir_opposite(d);
+                lp.wait_epoch[d] = p.steps_done * contributions(p, d);
+            } else {
+                lp.peer_out[d] = nullptr; lp.peer_flag[d] = nullptr; lp.wait_epoch[d] = 0;
+            }
+        }
+        lp.W = p.L.W; lp.H = p.L.H; lp.g = p.L.g; lp.lead = p.L.lead; lp.pitch = p.L.pitch;
+        lp.tilesX = p.tilesX; lp.tilesY = p.tilesY; lp.push_corners = p.push_corners;
+        const bool resid = (flags & 1) && s == nsteps - 1;
+        launch_step(p, lp, resid, st);
+        if (resid) {
+            sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials, p.grid,
+                                                   reinterpret_cast<double*>(p.base + kOffResid));
+            B200_CHECK_LAUNCH();
+        }
+        p.cur = outb;
+        p.steps_done += 1;
+    }
+    if (flags & 2) drain_impl(p, false, st);
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_drain(b2c_stencil* h, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    drain_impl(h->p, false, (cudaStream_t)stream);
+    B2C_CATCH
+}
+
+// Unfused halo exchange of the CURRENT buffer, phase 1: push my core edges
+// into the neighbours' ghost cells and bump their exchange counters.
+B2C_EXPORT int b2c_stencil_exchange_push(b2c_stencil* h, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    Plan& p = h->p;
+    XchgParams xp{};
+    xp.src = reinterpret_cast<const double*>(p.base + p.L.off_x[p.cur]);
+    xp.W = p.L.W; xp.H = p.L.H; xp.g = p.L.g; xp.lead = p.L.lead; xp.pitch = p.L.pitch;
+    for (int d = 0; d < 8; ++d) {
+        if (dir_active(p, d)) {
+            xp.peer[d] = reinterpret_cast<double*>(p.nbr[d] + p.L.off_x[p.cur]);
+            xp.peer_flag[d] = reinterpret_cast<uint64_t*>(p.nbr[d] + kOffXchgFlags) + dir_opposite(d);
+        }
+    }
+    halo_push1_kernel<<<8, 512, 0, (cudaStream_t)stream>>>(xp);
+    B200_CHECK_LAUNCH();
+    p.xchg_done += 1;
+    B2C_CATCH
+}
+
+// Phase 2: wait until every neighbour's push of the same exchange has landed.
+B2C_EXPORT int b2c_stencil_exchange_wait(b2c_stencil* h, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    drain_impl(h->p, true, (cudaStream_t)stream);
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_stencil_fill(b2c_stencil* h, int which, int region, double value, void* stream) {
+    // region: 0 = whole padded tile, 1 = core only
+    B2C_TRY
+    B200_REQUIRE(h && (which == 0 || which == 1), ERR_ARG, "bad argument");
+    Plan& p = h->p;
+    double* b = reinterpret_cast<double*>(p.base + p.L.off_x[which]);
+    int x0, y0, w, hh;
+    if (region == 0) { x0 = 0; y0 = 0; w = p.L.pitch; hh = p.L.rows; }
+    else { x0 = p.L.lead; y0 = p.L.g; w = p.L.W; hh = p.L.H; }
+    dim3 blk(64, 4), grd((w + 63) / 64, (hh + 3) / 4);
+    fill_rect_kernel<<<grd, blk, 0, (cudaStream_t)stream>>>(b, p.L.pitch, x0, y0, w, hh, value);
+    B200_CHECK_LAUNCH();
+    B2C_CATCH
+}
+
+// Returns the device status word (0 = healthy) after synchronising `stream`.
+B2C_EXPORT int b2c_stencil_status(b2c_stencil* h, void* stream, unsigned int* status) {
+    B2C_TRY
+    B200_REQUIRE(h && status, ERR_ARG, "null argument");
+    B200_CHECK_CUDA(cudaMemcpyAsync(status, h->p.base + kOffStatus, sizeof(unsigned),
+                                    cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    B2C_CATCH
+}
+
+}  // extern "C"

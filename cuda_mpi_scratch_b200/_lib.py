@@ -1,0 +1,129 @@
+"""ctypes binding of ``libb200comm.so`` (the C ABI in ``include/b200comm.h``).
+
+The library is built in-tree by :mod:`cuda_mpi_scratch_b200.build`.  If it is
+missing we try to build it once; if that fails the import raises -- there is
+no eager/PyTorch fallback for the kernels, by design: a GPU box without the
+native library must fail loudly rather than silently run something else.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "lib" / "libb200comm.so"
+
+
+class B200Error(RuntimeError):
+    """Raised when a native call returns a non-zero error class."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(message)
+        self.code = code
+
+
+class CommError(B200Error):
+    pass
+
+
+class CudaError(B200Error):
+    pass
+
+
+ERR_CUDA = 10
+ERR_TIMEOUT = 11
+ERR_TRUNCATE = 8
+
+
+def _load() -> C.CDLL:
+    if not LIB_PATH.exists() or os.environ.get("B200COMM_REBUILD") == "1":
+        from . import build as _build
+
+        _build.build()
+    return C.CDLL(str(LIB_PATH), mode=C.RTLD_GLOBAL)
+
+
+lib = _load()
+lib.b2c_last_error.restype = C.c_char_p
+lib.b2c_error_class_string.restype = C.c_char_p
+lib.b2c_error_class_string.argtypes = [C.c_int]
+
+
+def check(rc: int) -> None:
+    if rc == 0:
+        return
+    msg = lib.b2c_last_error().decode(errors="replace")
+    if not msg:
+        msg = lib.b2c_error_class_string(rc).decode()
+    if rc == ERR_CUDA:
+        raise CudaError(rc, msg)
+    raise CommError(rc, msg)
+
+
+def _proto(name: str, argtypes, restype=C.c_int):
+    fn = getattr(lib, name)
+    fn.argtypes = argtypes
+    fn.restype = restype
+    return fn
+
+
+vp = C.c_void_p
+sz = C.c_size_t
+i32 = C.c_int
+u64 = C.c_ulonglong
+pvp = C.POINTER(C.c_void_p)
+pi32 = C.POINTER(C.c_int)
+
+
+class StencilLayout(C.Structure):
+    _fields_ = [("W", i32), ("H", i32), ("radius", i32), ("ghost", i32), ("lead", i32),
+                ("pitch", i32), ("rows", i32), ("pad_bytes", sz), ("tile_bytes", sz),
+                ("off_buf0", sz), ("off_buf1", sz), ("off_red_slots", sz), ("total_bytes", sz)]
+
+
+class StencilInfo(C.Structure):
+    _fields_ = [("cur", i32), ("steps_done", u64), ("grid", i32), ("threads", i32),
+                ("nstages", i32), ("tiles_x", i32), ("tiles_y", i32), ("ncoef", i32),
+                ("launches_per_step", i32), ("smem_bytes", sz), ("buf", vp * 2),
+                ("resid", vp)]
+
+
+# ---- core
+_proto("b2c_set_error_mode", [i32])
+_proto("b2c_version", [])
+_proto("b2c_device_count", [pi32])
+_proto("b2c_bind_device", [i32, i32, i32, pi32])
+_proto("b2c_set_device", [i32])
+_proto("b2c_get_device", [pi32])
+_proto("b2c_device_synchronize", [])
+_proto("b2c_stream_synchronize", [vp])
+_proto("b2c_device_sm_count", [i32, pi32])
+_proto("b2c_malloc", [pvp, sz])
+_proto("b2c_free", [vp])
+_proto("b2c_memset_async", [vp, i32, sz, vp])
+_proto("b2c_memcpy_async", [vp, vp, sz, i32, vp])
+_proto("b2c_pinned_alloc", [pvp, sz])
+_proto("b2c_pinned_free", [vp])
+_proto("b2c_ipc_export", [vp, C.c_char_p])
+_proto("b2c_ipc_open", [C.c_char_p, pvp])
+_proto("b2c_ipc_close", [vp])
+_proto("b2c_enable_peer_access", [i32, i32])
+_proto("b2c_can_access_peer", [i32, i32, pi32])
+# ---- stencil
+_proto("b2c_stencil_layout", [i32, i32, i32, C.POINTER(StencilLayout)])
+_proto("b2c_stencil_create", [pvp, i32, i32, i32, i32, vp, C.POINTER(vp * 8), i32])
+_proto("b2c_stencil_destroy", [vp])
+_proto("b2c_stencil_set_coef", [vp, C.POINTER(C.c_double), i32, vp])
+_proto("b2c_stencil_set_timeout_ms", [vp, u64])
+_proto("b2c_stencil_info", [vp, C.POINTER(StencilInfo)])
+_proto("b2c_stencil_step", [vp, i32, i32, vp])
+_proto("b2c_stencil_drain", [vp, vp])
+_proto("b2c_stencil_exchange_push", [vp, vp])
+_proto("b2c_stencil_exchange_wait", [vp, vp])
+_proto("b2c_stencil_fill", [vp, i32, i32, C.c_double, vp])
+_proto("b2c_stencil_status", [vp, vp, C.POINTER(C.c_uint)])
+
+
+def have(name: str) -> bool:
+    return hasattr(lib, name)

@@ -1,0 +1,364 @@
+"""2-D Cartesian-decomposed stencil with the halo exchange fused into the update.
+
+Capability parity with the reference's stencil drivers
+(``stencil2d/mpi-2d-stencil-subarray-cuda.cu:77-179`` and the CPU twin
+``stencil2d/mpi-2d-stencil-subarray.cpp:35-100``): a periodic (or not)
+``Py x Px`` process grid, one ``H x W`` tile per rank surrounded by ghost
+cells of width ``stencil/2``, and the loop *exchange -> compute -> terminate?*.
+In the reference ``Compute()`` is an empty stub and the loop runs once
+(``:32-37``, ``:169-172``); here the update is a real radius-``R`` star (or
+3x3/5x5 box) stencil and one CUDA kernel per step does update **and** halo
+exchange (``csrc/stencil/stencil_kernel.cuh``).
+
+Coefficient order
+    star:  ``[centre, W1, E1, N1, S1, W2, E2, N2, S2, ...]`` (``4R+1`` values)
+    box:   ``(2R+1) x (2R+1)`` row-major, row 0 = north
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Callable, Sequence
+
+import torch
+
+from .. import _lib
+from ..parallel.cart import DIR_OFFSETS, PROC_NULL, CartTopology, dims_create
+from ..parallel.symmetric import SymmetricBuffer
+from ..parallel.world import LocalGroup, SingleWorld, World
+
+KIND = {"star": 0, "box": 1}
+
+
+def jacobi_coeffs(radius: int = 1, kind: str = "star") -> list[float]:
+    """Plain neighbour average (centre weight 0) -- the default."""
+    if kind == "star":
+        n = 4 * radius
+        return [0.0] + [1.0 / n] * n
+    side = 2 * radius + 1
+    n = side * side - 1
+    c = [1.0 / n] * (side * side)
+    c[side * side // 2] = 0.0
+    return c
+
+
+def layout(W: int, H: int, radius: int) -> _lib.StencilLayout:
+    lay = _lib.StencilLayout()
+    _lib.check(_lib.lib.b2c_stencil_layout(W, H, radius, C.byref(lay)))
+    return lay
+
+
+def _stream_ptr(device: int) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+class Stencil2D:
+    """One rank's tile + plan.  Build with :meth:`create` (one rank per process)
+    or :meth:`create_group` (virtual ranks in one process)."""
+
+    def __init__(self, rank: int, cart: CartTopology, tile_hw: tuple[int, int], radius: int,
+                 kind: str, symbuf: SymmetricBuffer, push_corners: bool, world: World | None):
+        self.rank, self.cart, self.world = rank, cart, world
+        self.H, self.W = int(tile_hw[0]), int(tile_hw[1])
+        self.radius, self.kind = radius, kind
+        self.symbuf = symbuf
+        self.device = symbuf.device
+        self.layout = layout(self.W, self.H, radius)
+        if symbuf.nbytes < self.layout.total_bytes:
+            raise ValueError("symmetric block too small for this tile")
+        self.neighbours = cart.neighbours8(rank)
+        nbr = (C.c_void_p * 8)()
+        for d, r in enumerate(self.neighbours):
+            nbr[d] = None if r == PROC_NULL else symbuf.peer_ptr(r)
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_create(C.byref(h), self.W, self.H, radius, KIND[kind],
+                                                   C.c_void_p(symbuf.local_ptr), C.byref(nbr),
+                                                   int(push_corners)))
+        self._h = h
+        self._coef_pinned = torch.empty(128, dtype=torch.float64).pin_memory() \
+            if torch.cuda.is_available() else torch.empty(128, dtype=torch.float64)
+        self._resid_pinned = torch.zeros(1, dtype=torch.float64).pin_memory() \
+            if torch.cuda.is_available() else torch.zeros(1, dtype=torch.float64)
+        self.kernel_launches = 0
+
+    # ------------------------------------------------------------ factories
+    @classmethod
+    def create(cls, world: World, tile_hw: tuple[int, int], radius: int = 1, kind: str = "star",
+               dims: Sequence[int] | None = None, periods=True,
+               push_corners: bool = True) -> "Stencil2D":
+        """Collective over ``world``: every rank gets an ``H x W`` tile."""
+        dims = tuple(dims) if dims is not None else dims_create(world.size, 2)
+        cart = CartTopology.create(dims, periods)
+        if cart.size != world.size:
+            raise ValueError(f"dims {dims} do not match world size {world.size}")
+        lay = layout(tile_hw[1], tile_hw[0], radius)
+        sym = SymmetricBuffer.allocate(world, lay.total_bytes)
+        return cls(world.rank, cart, tile_hw, radius, kind, sym, push_corners, world)
+
+    @classmethod
+    def create_group(cls, group: LocalGroup, tile_hw: tuple[int, int], radius: int = 1,
+                     kind: str = "star", dims: Sequence[int] | None = None, periods=True,
+                     push_corners: bool = True) -> "StencilGroup":
+        dims = tuple(dims) if dims is not None else dims_create(group.size, 2)
+        cart = CartTopology.create(dims, periods)
+        if cart.size != group.size:
+            raise ValueError(f"dims {dims} do not match group size {group.size}")
+        lay = layout(tile_hw[1], tile_hw[0], radius)
+        syms = SymmetricBuffer.allocate_local(group, lay.total_bytes)
+        return StencilGroup([cls(r, cart, tile_hw, radius, kind, syms[r], push_corners, None)
+                             for r in range(group.size)])
+
+    # ------------------------------------------------------------ views
+    def info(self) -> _lib.StencilInfo:
+        inf = _lib.StencilInfo()
+        _lib.check(_lib.lib.b2c_stencil_info(self._h, C.byref(inf)))
+        return inf
+
+    def _buffer(self, which: int) -> torch.Tensor:
+        L = self.layout
+        off = L.off_buf0 if which == 0 else L.off_buf1
+        return self.symbuf.tensor(off, (L.rows, L.pitch), torch.float64)
+
+    @property
+    def current(self) -> int:
+        return self.info().cur
+
+    @property
+    def padded(self) -> torch.Tensor:
+        """Whole padded buffer holding the current state: ``rows x pitch``."""
+        return self._buffer(self.current)
+
+    @property
+    def tile(self) -> torch.Tensor:
+        """Core + ghost cells of the current state: ``(H+2g) x (W+2g)`` view."""
+        L = self.layout
+        return self.padded[:, L.lead - L.ghost: L.lead + L.W + L.ghost]
+
+    @property
+    def core(self) -> torch.Tensor:
+        """The ``H x W`` core of the current state (writable view)."""
+        L = self.layout
+        return self.padded[L.ghost: L.ghost + L.H, L.lead: L.lead + L.W]
+
+    # ------------------------------------------------------------ set-up
+    def fill(self, core_value: float | None = None, ghost_value: float | None = None) -> None:
+        """Initialise BOTH buffers (the reference fills the tile with -1 and the
+        core with the rank id, ``mpi-2d-stencil-subarray-cuda.cu:148-159``)."""
+        st = _stream_ptr(self.device)
+        with torch.cuda.device(self.device):
+            for b in (0, 1):
+                if ghost_value is not None:
+                    _lib.check(_lib.lib.b2c_stencil_fill(self._h, b, 0, float(ghost_value), st))
+                if core_value is not None:
+                    _lib.check(_lib.lib.b2c_stencil_fill(self._h, b, 1, float(core_value), st))
+        self.kernel_launches += 2 * ((ghost_value is not None) + (core_value is not None))
+
+    def set_coeffs(self, coeffs: Sequence[float]) -> None:
+        """Copy stencil coefficients host(pinned) -> device on the current stream."""
+        n = len(coeffs)
+        self._coef_pinned[:n] = torch.as_tensor(coeffs, dtype=torch.float64)
+        ptr = C.cast(self._coef_pinned.data_ptr(), C.POINTER(C.c_double))
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_set_coef(self._h, ptr, n, _stream_ptr(self.device)))
+
+    # ------------------------------------------------------------ exchange
+    def exchange_push(self) -> None:
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_exchange_push(self._h, _stream_ptr(self.device)))
+        self.kernel_launches += 1
+
+    def exchange_wait(self) -> None:
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_exchange_wait(self._h, _stream_ptr(self.device)))
+        self.kernel_launches += 1
+
+    def exchange(self) -> None:
+        """Unfused halo exchange of the current state (``ExchangeData``,
+        ``stencil2d/stencil2D.h:363-377``).  One rank per process only; virtual
+        ranks use :meth:`StencilGroup.exchange`."""
+        if self.world is None:
+            raise RuntimeError("use StencilGroup.exchange() for virtual ranks")
+        self.world.barrier()  # peers are done touching the buffers
+        self.exchange_push()
+        self.exchange_wait()
+
+    # ------------------------------------------------------------ stepping
+    def step(self, nsteps: int = 1, residual: bool = False, drain: bool = True) -> None:
+        """Enqueue ``nsteps`` fused update+halo steps on the current stream."""
+        flags = (1 if residual else 0) | (2 if drain else 0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_step(self._h, nsteps, flags, _stream_ptr(self.device)))
+        self.kernel_launches += nsteps + (1 if residual and nsteps else 0) + (1 if drain else 0)
+
+    def drain(self) -> None:
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_drain(self._h, _stream_ptr(self.device)))
+        self.kernel_launches += 1
+
+    def local_residual_async(self) -> torch.Tensor:
+        """Start the D2H copy of the last step's local sum of squared updates into
+        pinned memory; valid after the stream is synchronised."""
+        inf = self.info()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_memcpy_async(C.c_void_p(self._resid_pinned.data_ptr()),
+                                                 C.c_void_p(inf.resid), 8, 2,
+                                                 _stream_ptr(self.device)))
+        return self._resid_pinned
+
+    def check(self) -> None:
+        """Synchronise and raise if a device-side wait timed out."""
+        st = C.c_uint(0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_status(self._h, _stream_ptr(self.device), C.byref(st)))
+        if st.value & 1:
+            raise _lib.CommError(_lib.ERR_TIMEOUT, "halo flag wait timed out on the device "
+                                 f"(rank {self.rank}): a neighbour did not deliver")
+
+    def run(self, steps: int | None = None, until: Callable[[float], bool] | None = None,
+            check_every: int = 10, max_steps: int = 1 << 30) -> tuple[int, float | None]:
+        """``do { exchange; compute } while (!terminate)`` -- fused.
+
+        ``steps``: run exactly that many.  ``until(residual_l2)``: evaluate the
+        global residual every ``check_every`` steps and stop when it returns
+        True (the reference's ``TerminateCondition``,
+        ``mpi-2d-stencil-subarray-cuda.cu:36-37``, which always returns true).
+        Returns ``(steps_run, last_residual_or_None)``.
+        """
+        if until is None:
+            self.step(int(steps or 0))
+            return int(steps or 0), None
+        done, res = 0, None
+        while done < max_steps:
+            n = min(check_every, max_steps - done)
+            self.step(n, residual=True)
+            done += n
+            res = self.residual()
+            if until(res):
+                break
+        return done, res
+
+    def residual(self) -> float:
+        """Global L2 norm of the last update (synchronises)."""
+        buf = self.local_residual_async()
+        torch.cuda.current_stream(self.device).synchronize()
+        s = float(buf.item())
+        if self.world is not None and self.world.size > 1:
+            s = self.world.allreduce_sum(s)
+        return s ** 0.5
+
+    # ------------------------------------------------------------ output
+    def dump_str(self, fmt: str = "{:g}") -> str:
+        """Tile incl. ghosts, one row per line, every value followed by a space
+        -- the format of ``Print`` (``stencil2d/stencil2D.h:92-102``)."""
+        t = self.tile.cpu()
+        return "".join("".join(fmt.format(v) + " " for v in row.tolist()) + "\n" for row in t)
+
+    def close(self) -> None:
+        if self._h:
+            _lib.lib.b2c_stencil_destroy(self._h)
+            self._h = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class StencilGroup:
+    """All virtual ranks of a :class:`LocalGroup`, stepped in lock-step.
+
+    Within one process every launch goes into a stream in program order, so
+    rank ``r``'s step ``s+1`` is always enqueued after every rank's step
+    ``s``: no kernel ever spins on a flag whose producer has not been launched
+    (the constraint spelled out in the profiling guide for single-GPU runs).
+    """
+
+    def __init__(self, ranks: list[Stencil2D]):
+        self.ranks = ranks
+
+    def __len__(self):
+        return len(self.ranks)
+
+    def __getitem__(self, i):
+        return self.ranks[i]
+
+    def sync(self) -> None:
+        for d in {s.device for s in self.ranks}:
+            torch.cuda.synchronize(d)
+
+    def exchange(self) -> None:
+        self.sync()
+        for s in self.ranks:
+            s.exchange_push()
+        self.sync()
+        for s in self.ranks:
+            s.exchange_wait()
+        self.sync()
+
+    def step(self, nsteps: int = 1, residual: bool = False) -> None:
+        multi_dev = len({s.device for s in self.ranks}) > 1
+        for i in range(nsteps):
+            last = i == nsteps - 1
+            for s in self.ranks:
+                s.step(1, residual=residual and last, drain=False)
+            if multi_dev:
+                # different devices run concurrently: keep ranks within one step
+                # of each other exactly like separate processes would be
+                pass
+        if multi_dev:
+            self.sync()
+        for s in self.ranks:
+            s.drain()
+
+    def residual(self) -> float:
+        bufs = [s.local_residual_async() for s in self.ranks]
+        self.sync()
+        return sum(float(b.item()) for b in bufs) ** 0.5
+
+    def check(self) -> None:
+        for s in self.ranks:
+            s.check()
+
+    def gather_global(self) -> torch.Tensor:
+        """Assemble the global grid from the cores (CPU tensor)."""
+        cart = self.ranks[0].cart
+        rows, cols = cart.dims
+        H, W = self.ranks[0].H, self.ranks[0].W
+        out = torch.empty(rows * H, cols * W, dtype=torch.float64)
+        for s in self.ranks:
+            r, c = cart.coords(s.rank)
+            out[r * H:(r + 1) * H, c * W:(c + 1) * W] = s.core.cpu()
+        return out
+
+    def scatter_global(self, g: torch.Tensor) -> None:
+        """Set every rank's core (both buffers are NOT touched: only current)."""
+        cart = self.ranks[0].cart
+        H, W = self.ranks[0].H, self.ranks[0].W
+        for s in self.ranks:
+            r, c = cart.coords(s.rank)
+            s.core.copy_(g[r * H:(r + 1) * H, c * W:(c + 1) * W].to(s.core.device))
+
+
+# ------------------------------------------------------------------ oracle
+def reference_step(grid: torch.Tensor, coeffs: Sequence[float], radius: int = 1,
+                   kind: str = "star") -> torch.Tensor:
+    """Plain PyTorch fp64 periodic stencil on the GLOBAL grid (test oracle)."""
+    g = grid.to(torch.float64)
+    out = torch.zeros_like(g)
+    if kind == "star":
+        out += coeffs[0] * g
+        for k in range(1, radius + 1):
+            b = 1 + 4 * (k - 1)
+            out += coeffs[b + 0] * torch.roll(g, k, dims=1)    # west neighbour
+            out += coeffs[b + 1] * torch.roll(g, -k, dims=1)   # east
+            out += coeffs[b + 2] * torch.roll(g, k, dims=0)    # north
+            out += coeffs[b + 3] * torch.roll(g, -k, dims=0)   # south
+    else:
+        side = 2 * radius + 1
+        for iy in range(side):
+            for ix in range(side):
+                w = coeffs[iy * side + ix]
+                if w != 0.0:
+                    out += w * torch.roll(g, (radius - iy, radius - ix), dims=(0, 1))
+    return out

@@ -1,0 +1,118 @@
+"""Device-side timing and clock sampling.
+
+The reference times with ``clock()`` (CPU time, compared across processes,
+``mpicuda3.cu:176-179,315-325``) and a single un-warmed ``MPI_Wtime`` bracket
+(``test-benchmark/mpi-pingpong-gpu.cpp:51-54``) -- SURVEY.md 2.7 #12.  Here
+every number is taken with CUDA events on the launching stream after warm-up,
+and multi-rank numbers are the max over ranks.
+"""
+from __future__ import annotations
+
+import statistics
+import subprocess
+import threading
+from typing import Callable
+
+import torch
+
+_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+
+class L2Flusher:
+    """Writes a buffer larger than the 126 MB L2 between timed iterations."""
+
+    def __init__(self, device: int, nbytes: int = 256 << 20):
+        self.buf = torch.empty(nbytes // 4, dtype=torch.int32, device=torch.device("cuda", device))
+        self._v = 0
+
+    def __call__(self) -> None:
+        self._v += 1
+        self.buf.fill_(self._v)
+
+
+def time_cuda_ms(fn: Callable[[], None], warmup: int = 3, iters: int = 10, device: int = 0,
+                 flush: L2Flusher | None = None) -> list[float]:
+    """Per-iteration device time of ``fn`` in ms (CUDA events, after warm-up)."""
+    stream = torch.cuda.current_stream(device)
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize(device)
+    out = []
+    for _ in range(iters):
+        if flush is not None:
+            flush()
+        a = torch.cuda.Event(enable_timing=True)
+        b = torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        fn()
+        b.record(stream)
+        b.synchronize()
+        out.append(a.elapsed_time(b))
+    return out
+
+
+class ClockSampler:
+    """Samples ``nvidia-smi`` clocks/throttle reasons in the background while a
+    timed region runs (the recipe in B200_PROFILING.md)."""
+
+    def __init__(self, device: int = 0, period_ms: int = 100):
+        self.device, self.period_ms = device, period_ms
+        self.rows: list[list[str]] = []
+        self._proc: subprocess.Popen | None = None
+        self._thr: threading.Thread | None = None
+
+    def start(self) -> "ClockSampler":
+        try:
+            self._proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={_QUERY}", "--format=csv,noheader,nounits",
+                 "-i", str(self.device), "-lms", str(self.period_ms)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self._proc = None
+            return self
+        self._thr = threading.Thread(target=self._pump, daemon=True)
+        self._thr.start()
+        return self
+
+    def _pump(self) -> None:
+        assert self._proc is not None and self._proc.stdout is not None
+        for line in self._proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 9:
+                self.rows.append(parts)
+
+    def stop(self) -> dict:
+        if self._proc is not None:
+            self._proc.terminate()
+            try:
+                self._proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:  # pragma: no cover
+                self._proc.kill()
+        if self._thr is not None:
+            self._thr.join(timeout=2)
+        return self.summary()
+
+    def summary(self) -> dict:
+        sm, smax, power = [], [], []
+        reasons: set[str] = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                smax.append(float(r[2]))
+                power.append(float(r[3]))
+            except ValueError:
+                continue
+            for name, val in zip(names, r[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        # "under load": samples in the upper half of the power range
+        pmid = (max(power) + min(power)) / 2
+        load = [s for s, p in zip(sm, power) if p >= pmid] or sm
+        return {"sm_mhz": statistics.median(load), "sm_max_mhz": max(smax),
+                "reasons": sorted(reasons), "samples": len(sm),
+                "power_w_max": max(power)}
