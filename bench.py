@@ -95,10 +95,14 @@ def main(argv=None) -> int:
 
     stream = torch.cuda.current_stream(dev)
     # ---------------- device-timed: K fused steps ----------------
-    st.step(args.warmup)
+    # clocks are sampled from before the warm-up to the end of the e2e loop so
+    # that several samples fall under load even when K steps take a few ms
+    sampler = ClockSampler(dev, period_ms=20).start() if world.rank == 0 else None
+    if sampler is not None:
+        sampler.wait_first(2.0)
+    st.step(max(args.warmup, 3))
     torch.cuda.synchronize(dev)
     world.barrier()
-    sampler = ClockSampler(dev).start() if world.rank == 0 else None
     launches0 = st.kernel_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)

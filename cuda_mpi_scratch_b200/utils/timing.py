@@ -76,6 +76,13 @@ class ClockSampler:
         self._thr.start()
         return self
 
+    def wait_first(self, timeout_s: float = 2.0) -> None:
+        """Block until the first sample arrived (nvidia-smi takes a while to start)."""
+        import time
+        t0 = time.perf_counter()
+        while not self.rows and time.perf_counter() - t0 < timeout_s:
+            time.sleep(0.01)
+
     def _pump(self) -> None:
         assert self._proc is not None and self._proc.stdout is not None
         for line in self._proc.stdout:

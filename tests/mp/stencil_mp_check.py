@@ -1,0 +1,65 @@
+"""Multi-process (one rank per GPU) check of the fused stencil, run under torchrun:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29533 tests/mp/stencil_mp_check.py
+
+Every rank compares its tile with the PyTorch fp64 oracle of the GLOBAL periodic grid."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+
+import torch
+
+import cuda_mpi_scratch_b200 as cms
+from cuda_mpi_scratch_b200.models.stencil2d import Stencil2D, jacobi_coeffs, reference_step
+
+
+def main():
+    world = cms.init()
+    dims = cms.dims_create(world.size)
+    fails = 0
+    for (th, tw, R, kind, steps) in [(64, 256, 1, "star", 7), (96, 384, 2, "star", 5),
+                                      (50, 200, 1, "box", 4), (1024, 2048, 1, "star", 20)]:
+        st = Stencil2D.create(world, (th, tw), R, kind, dims=dims)
+        g = torch.Generator().manual_seed(1234)
+        glob = torch.rand(dims[0] * th, dims[1] * tw, dtype=torch.float64, generator=g)
+        r, c = st.cart.coords(world.rank)
+        st.fill(0.0, 0.0)
+        st.core.copy_(glob[r * th:(r + 1) * th, c * tw:(c + 1) * tw])
+        torch.cuda.synchronize()
+        st.exchange()
+        st.step(steps, residual=True)
+        res = st.residual()
+        st.check()
+        exp, prev = glob, None
+        co = jacobi_coeffs(R, kind)
+        for _ in range(steps):
+            prev = exp
+            exp = reference_step(exp, co, R, kind)
+        want = exp[r * th:(r + 1) * th, c * tw:(c + 1) * tw]
+        err = float((st.core.cpu() - want).abs().max())
+        want_res = float(((exp - prev) ** 2).sum().sqrt())
+        ok = err < 1e-12 and abs(res - want_res) <= 1e-10 * want_res
+        # ghosts of the current buffer must hold the neighbours' cores after the drain
+        tile = st.tile.cpu()
+        gp = torch.roll(exp, (R - r * th, R - c * tw), dims=(0, 1))[: th + 2 * R, : tw + 2 * R]
+        if kind == "star":  # corners are exchanged too (push_corners=True by default)
+            pass
+        gerr = float((tile - gp).abs().max())
+        ok = ok and gerr < 1e-12
+        fails += 0 if ok else 1
+        print(f"rank {world.rank} dims {dims} tile {th}x{tw} R{R} {kind}: err {err:.2e} "
+              f"ghost err {gerr:.2e} resid {res:.6e} (want {want_res:.6e}) {'OK' if ok else 'FAIL'}",
+              flush=True)
+        world.barrier()
+        st.close()
+    tot = world.allreduce_sum(float(fails))
+    if world.rank == 0:
+        print("MP_STENCIL_CHECK", "PASSED" if tot == 0 else f"FAILED ({int(tot)})", flush=True)
+    world.finalize()
+    return 0 if tot == 0 else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
