@@ -16,9 +16,17 @@
 //     shared memory with a register sliding window and write 16-byte aligned
 //     rows of the output tile;
 //   * consumers of a boundary tile also store the freshly computed edge cells
-//     straight into the NEIGHBOUR GPU's ghost cells (peer addresses over
-//     NVLink), then one thread release-increments that neighbour's per-direction
-//     epoch counter (red.release.sys);
+//     into the NEIGHBOUR GPU's memory (peer addresses over NVLink): edge ROWS
+//     go straight into the neighbour's ghost rows (1 KiB contiguous per tile
+//     row); edge COLUMNS are staged in shared memory and written as one
+//     coalesced burst into a contiguous per-neighbour "landing" buffer
+//     [padded row][g] -- strided 8-byte stores over NVLink were measured at
+//     ~8 ns EACH (0.28 ms per step for 2 x 16384 cells), so columns never travel
+//     strided.  One thread then release-increments the neighbour's
+//     per-direction epoch counter (red.release.sys);
+//   * the consumer of a west/east boundary tile patches the ghost columns of its
+//     TMA box in shared memory from its landing buffer (the in-grid ghost
+//     columns are refreshed from the landing buffers only when a run drains);
 //   * before a boundary tile is loaded, the producer acquires (ld.acquire.sys)
 //     the epoch counters of the directions whose ghost cells the tile reads --
 //     the device-side replacement of MPI_Waitall.  The same acquire also
@@ -51,6 +59,14 @@ __host__ __device__ constexpr int dir_dx(int d) {
     return (d == 0 || d == 3 || d == 5) ? -1 : ((d == 1 || d == 6) ? 0 : 1);
 }
 __host__ __device__ constexpr int dir_opposite(int d) { return 7 - d; }
+// Column landing buffers are indexed [kLandLead + padded_row - g][R] so that
+// the burst of core row 0 starts on a 128-byte line.
+constexpr int kLandLead = 16;
+__host__ __device__ constexpr size_t land_index(int padded_row, int g, int R) {
+    return (size_t)(padded_row - g + kLandLead) * R;
+}
+// directions with a column (east/west) component: NW NE W E SW SE
+constexpr unsigned kColDirs = (1u << 0) | (1u << 2) | (1u << 3) | (1u << 4) | (1u << 5) | (1u << 7);
 
 template <int R>
 struct Geo {
@@ -66,6 +82,8 @@ struct LaunchParams {
     const double* in;          // local padded input buffer (same layout)
     const double* coef;        // device coefficients (layout: see Stencil2D docs)
     double* peer_out[8];       // neighbour's output buffer per direction (nullptr: none)
+    double* peer_land[8];      // dx != 0 only: neighbour's column landing buffer (out parity)
+    const double* my_land[2];  // my west / east column landing buffers (in parity)
     uint64_t* peer_flag[8];    // neighbour's epoch counter that I bump per direction
     const uint64_t* my_flags;  // my 8 epoch counters (indexed by the direction data comes from)
     uint64_t wait_epoch[8];    // value my_flags[d] must reach before ghost cells of d are read
@@ -78,6 +96,7 @@ struct LaunchParams {
     int pitch;                 // elements per padded row
     int tilesX, tilesY;
     int push_corners;          // also exchange the 4 corner blocks
+    int debug;                 // bit0: skip column pushes, bit1: skip flag waits (experiments only)
 };
 
 __device__ __forceinline__ void decode_tile(int i, int nbx, int nby, int& tx, int& ty) {
@@ -132,6 +151,8 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + NSTAGES * G::STAGE_BYTES);
     uint64_t* empty = full + NSTAGES;
     __shared__ double red_smem[kConsumers / 32];
+    __shared__ double colstage[2][2][kTileH][R];   // [parity][west|east][tile row][k]
+    int bparity = 0;                                // alternates per boundary tile
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -158,7 +179,7 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                 int tx, ty;
                 decode_tile(i, nbx, nby, tx, ty);
                 const unsigned act = active_dirs(P, edge_mask(tx, ty, nbx, nby));
-                if (act) {
+                if (act && !(P.debug & 2)) {
                     const uint64_t t0 = ptx::globaltimer_ns();
                     for (int d = 0; d < 8; ++d) {
                         if (!(act >> d & 1u)) continue;
@@ -206,6 +227,25 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
 
         ptx::mbar_wait(&full[stage], phase);
         const double* box = reinterpret_cast<const double*>(smem + stage * G::STAGE_BYTES);
+        if (act & kColDirs) {
+            // Ghost columns of this box come from the landing buffers, not from the
+            // grid: one element per thread, rows = padded rows ty*TH .. +BOXH.
+            double* wbox = reinterpret_cast<double*>(smem + stage * G::STAGE_BYTES);
+            for (int e = tid; e < 2 * G::BOXH * R; e += kConsumers) {
+                const int side = e / (G::BOXH * R), rem = e % (G::BOXH * R);
+                const int j = rem / R, k = rem % R;
+                const int pr = ty * kTileH + j;                 // padded row (g == R)
+                if (pr >= P.H + 2 * R) continue;
+                const int vd = pr < R ? (side ? NE : NW) : (pr >= P.H + R ? (side ? SE : SW)
+                                                                          : (side ? E_ : W_));
+                if (!(act >> vd & 1u)) continue;
+                const double v = P.my_land[side][land_index(pr, R, R) + k];
+                const int col = side ? G::RA + (P.W - tx * kTileW) + k : G::RA - R + k;
+                wbox[j * G::BOXW + col] = v;
+            }
+            ptx::fence_proxy_async();   // generic smem writes vs the next TMA into this stage
+            ptx::named_bar_sync(3, kConsumers);
+        }
         // box(row, col): row = tile row + R, col = tile col + RA
         const double* mycol = box + c0 + G::RA;
 
@@ -307,38 +347,65 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
             }
         }
         if (act) {
-            // -------- halo push: edge cells go straight to the neighbours --------
+            // -------- halo push --------
             if (gx < P.W) {
+                // edge rows: straight into the neighbour's ghost rows (contiguous)
 #pragma unroll 1
-                for (int d = 0; d < 8; ++d) {
+                for (int d = N; d <= S; d += S - N) {
                     if (!(act >> d & 1u)) continue;
-                    const int dy = dir_dy(d), dx = dir_dx(d);
+                    const int dy = dir_dy(d);
                     double* pb = P.peer_out[d];
 #pragma unroll
                     for (int y = 0; y < kRowsPerThread; ++y) {
                         const int gy = ty * kTileH + r0 + y;
                         if (gy >= P.H) continue;
-                        const bool rowok = dy < 0 ? gy < P.g : (dy > 0 ? gy >= P.H - P.g : true);
-                        if (!rowok) continue;
-                        double* prow = pb + (size_t)(gy + P.g - dy * P.H) * P.pitch + P.lead -
-                                       dx * P.W;
-                        if (dx == 0) {
-                            *reinterpret_cast<double2*>(prow + gx) = res[y];
-                        } else {
-                            const bool ok0 = dx < 0 ? gx < P.g : gx >= P.W - P.g;
-                            const bool ok1 = dx < 0 ? gx + 1 < P.g : gx + 1 >= P.W - P.g;
-                            if (ok0) prow[gx] = res[y].x;
-                            if (ok1) prow[gx + 1] = res[y].y;
+                        if (dy < 0 ? gy >= P.g : gy < P.H - P.g) continue;
+                        double* prow = pb + (size_t)(gy + P.g - dy * P.H) * P.pitch + P.lead;
+                        *reinterpret_cast<double2*>(prow + gx) = res[y];
+                    }
+                }
+                // edge columns: stage in shared memory
+                if (act & kColDirs) {
+#pragma unroll
+                    for (int y = 0; y < kRowsPerThread; ++y) {
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            const int x = gx + q;
+                            const double v = q ? res[y].y : res[y].x;
+                            if (x < P.g) colstage[bparity][0][r0 + y][x] = v;
+                            if (x >= P.W - P.g && x < P.W) colstage[bparity][1][r0 + y][x - (P.W - P.g)] = v;
                         }
                     }
                 }
             }
-            // every consumer's peer stores happen-before thread 0's release
+            // every consumer's peer stores / staging writes happen-before warp 0's work
             ptx::named_bar_sync(1, kConsumers);
-            if (tid == 0) {
-                for (int d = 0; d < 8; ++d)
-                    if (act >> d & 1u) ptx::red_add_release_sys(P.peer_flag[d], 1ull);
+            if (warp == 0) {
+                if ((act & kColDirs) && !(P.debug & 1)) {
+                    // coalesced bursts into the neighbours' landing buffers
+                    const int rows_here = min(kTileH, P.H - ty * kTileH);
+                    for (int d = 0; d < 8; ++d) {
+                        const int dy = dir_dy(d), dx = dir_dx(d);
+                        if (dx == 0 || !(act >> d & 1u)) continue;
+                        const int side = dx < 0 ? 0 : 1;
+                        // tile rows [ya, yb) take part in direction d
+                        int ya = 0, yb = rows_here;
+                        if (dy < 0) yb = min(yb, P.g - ty * kTileH);
+                        if (dy > 0) ya = max(ya, P.H - P.g - ty * kTileH);
+                        const int n = (yb - ya) * R;
+                        double* dst = P.peer_land[d] +
+                                      land_index(ty * kTileH + ya + P.g - dy * P.H, R, R);
+                        const double* src = &colstage[bparity][side][ya][0];
+                        for (int e = lane; e < n; e += 32) dst[e] = src[e];
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    for (int d = 0; d < 8; ++d)
+                        if (act >> d & 1u) ptx::red_add_release_sys(P.peer_flag[d], 1ull);
+                }
             }
+            bparity ^= 1;
         }
         if (++stage == NSTAGES) { stage = 0; phase ^= 1u; }
     }

@@ -10,6 +10,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -36,6 +37,8 @@ struct Layout {
     int W, H, R, g, lead, pitch, rows;
     size_t tile_bytes;   // one padded buffer
     size_t off_x[2];     // offsets of the two buffers inside the symmetric block
+    size_t land_bytes;   // one column landing buffer
+    size_t off_land[2][2];  // [buffer parity][0 west ghost | 1 east ghost]
     size_t total_bytes;
 };
 
@@ -49,7 +52,11 @@ static Layout make_layout(int W, int H, int R) {
     L.tile_bytes = ((size_t)L.pitch * L.rows * sizeof(double) + 1023) & ~(size_t)1023;
     L.off_x[0] = kPadBytes;
     L.off_x[1] = kPadBytes + L.tile_bytes;
-    L.total_bytes = kPadBytes + 2 * L.tile_bytes;
+    L.land_bytes = ((size_t)(L.rows + kLandLead) * R * sizeof(double) + 1023) & ~(size_t)1023;
+    size_t off = kPadBytes + 2 * L.tile_bytes;
+    for (int b = 0; b < 2; ++b)
+        for (int sd = 0; sd < 2; ++sd) { L.off_land[b][sd] = off; off += L.land_bytes; }
+    L.total_bytes = off;
     return L;
 }
 
@@ -57,7 +64,8 @@ static Layout make_layout(int W, int H, int R) {
 
 struct XchgParams {
     const double* src;        // my current buffer
-    double* peer[8];          // neighbours' current buffers
+    double* peer[8];          // neighbours' current buffers (row directions N, S)
+    double* peer_land[8];     // neighbours' landing buffers (directions with a column part)
     uint64_t* peer_flag[8];   // neighbours' xchg counters (slot opposite(d))
     int W, H, g, lead, pitch;
 };
@@ -77,10 +85,36 @@ __global__ void halo_push1_kernel(const __grid_constant__ XchgParams P) {
     for (long i = threadIdx.x; i < n; i += blockDim.x) {
         const int y = y0 + (int)(i / cols), x = x0 + (int)(i % cols);
         const double v = P.src[(size_t)(y + P.g) * P.pitch + P.lead + x];
-        pb[(size_t)(y + P.g - dy * P.H) * P.pitch + P.lead + x - dx * P.W] = v;
+        if (dx == 0)
+            pb[(size_t)(y + P.g - dy * P.H) * P.pitch + P.lead + x] = v;
+        else   // columns land contiguously: [padded row][k]
+            P.peer_land[d][land_index(y + P.g - dy * P.H, P.g, P.g) + (x - x0)] = v;
     }
     __syncthreads();
     if (threadIdx.x == 0) ptx::red_add_release_sys(P.peer_flag[d], 1ull);
+}
+
+struct UnpackParams {
+    double* grid;             // my current buffer
+    const double* land[2];    // my west / east landing buffers of the same parity
+    int active[8];            // which directions delivered data
+    int W, H, g, lead, pitch;
+};
+
+// Landing buffers -> in-grid ghost columns (local, after a drain/exchange wait),
+// so that the tile a user sees always carries complete ghost cells.
+__global__ void land_unpack_kernel(const __grid_constant__ UnpackParams P) {
+    const int rows = P.H + 2 * P.g;
+    const int n = 2 * rows * P.g;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const int side = e / (rows * P.g), rem = e % (rows * P.g);
+        const int pr = rem / P.g, k = rem % P.g;
+        const int vd = pr < P.g ? (side ? NE : NW)
+                                : (pr >= P.H + P.g ? (side ? SE : SW) : (side ? E_ : W_));
+        if (!P.active[vd]) continue;
+        const int col = side ? P.lead + P.W + k : P.lead - P.g + k;
+        P.grid[(size_t)pr * P.pitch + col] = P.land[side][land_index(pr, P.g, P.g) + k];
+    }
 }
 
 struct WaitParams {
@@ -229,6 +263,9 @@ B2C_EXPORT int b2c_stencil_layout(int W, int H, int R, b2c_stencil_layout_t* out
     B200_REQUIRE(W >= 2 && H >= 1 && (W % 2) == 0, ERR_ARG, "tile width must be even and >= 2");
     B200_REQUIRE(R >= 1 && R <= kMaxRadius, ERR_ARG, "radius must be in [1,4]");
     B200_REQUIRE(W >= R && H >= R, ERR_ARG, "tile smaller than the stencil radius");
+    // an edge strip of width R must not straddle two kernel tiles (128 x 32 cells)
+    B200_REQUIRE((W % kTileW == 0 || W % kTileW >= R) && (H % kTileH == 0 || H % kTileH >= R),
+                 ERR_ARG, "W mod 128 and H mod 32 must be 0 or >= radius");
     Layout L = make_layout(W, H, R);
     out->W = W; out->H = H; out->radius = R; out->ghost = L.g; out->lead = L.lead;
     out->pitch = L.pitch; out->rows = L.rows; out->tile_bytes = L.tile_bytes;
@@ -351,6 +388,21 @@ static void drain_impl(Plan& p, bool xchg, cudaStream_t st) {
     if (!any) return;
     flag_wait_kernel<<<1, 32, 0, st>>>(wp);
     B200_CHECK_LAUNCH();
+    // refresh the in-grid ghost columns of the current buffer from the landing buffers
+    UnpackParams up{};
+    up.grid = reinterpret_cast<double*>(p.base + p.L.off_x[p.cur]);
+    up.land[0] = reinterpret_cast<const double*>(p.base + p.L.off_land[p.cur][0]);
+    up.land[1] = reinterpret_cast<const double*>(p.base + p.L.off_land[p.cur][1]);
+    bool cols = false;
+    for (int d = 0; d < 8; ++d) {
+        up.active[d] = dir_active(p, d) && dir_dx(d) != 0 && wp.epoch[d] != 0;
+        cols = cols || up.active[d];
+    }
+    if (!cols) return;
+    up.W = p.L.W; up.H = p.L.H; up.g = p.L.g; up.lead = p.L.lead; up.pitch = p.L.pitch;
+    const int n = 2 * p.L.rows * p.L.g;
+    land_unpack_kernel<<<(n + 255) / 256 > 64 ? 64 : (n + 255) / 256, 256, 0, st>>>(up);
+    B200_CHECK_LAUNCH();
 }
 
 // Launch `nsteps` fused steps.  flags: bit0 = compute the residual of the LAST
@@ -375,15 +427,22 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         for (int d = 0; d < 8; ++d) {
             if (dir_active(p, d)) {
                 lp.peer_out[d] = reinterpret_cast<double*>(p.nbr[d] + p.L.off_x[outb]);
+                // my west edge becomes the neighbour's EAST ghost and vice versa
+                lp.peer_land[d] = dir_dx(d) == 0 ? nullptr :
+                    reinterpret_cast<double*>(p.nbr[d] + p.L.off_land[outb][dir_dx(d) < 0 ? 1 : 0]);
                 lp.peer_flag[d] =
                     reinterpret_cast<uint64_t*>(p.nbr[d] + kOffStepFlags) + dir_opposite(d);
                 lp.wait_epoch[d] = p.steps_done * contributions(p, d);
             } else {
-                lp.peer_out[d] = nullptr; lp.peer_flag[d] = nullptr; lp.wait_epoch[d] = 0;
+                lp.peer_out[d] = nullptr; lp.peer_land[d] = nullptr; lp.peer_flag[d] = nullptr;
+                lp.wait_epoch[d] = 0;
             }
         }
+        lp.my_land[0] = reinterpret_cast<const double*>(p.base + p.L.off_land[in][0]);
+        lp.my_land[1] = reinterpret_cast<const double*>(p.base + p.L.off_land[in][1]);
         lp.W = p.L.W; lp.H = p.L.H; lp.g = p.L.g; lp.lead = p.L.lead; lp.pitch = p.L.pitch;
         lp.tilesX = p.tilesX; lp.tilesY = p.tilesY; lp.push_corners = p.push_corners;
+        { const char* dbg = std::getenv("B2C_STENCIL_DEBUG"); lp.debug = dbg ? std::atoi(dbg) : 0; }
         const bool resid = (flags & 1) && s == nsteps - 1;
         launch_step(p, lp, resid, st);
         if (resid) {
@@ -417,6 +476,8 @@ B2C_EXPORT int b2c_stencil_exchange_push(b2c_stencil* h, void* stream) {
     for (int d = 0; d < 8; ++d) {
         if (dir_active(p, d)) {
             xp.peer[d] = reinterpret_cast<double*>(p.nbr[d] + p.L.off_x[p.cur]);
+            xp.peer_land[d] = dir_dx(d) == 0 ? nullptr :
+                reinterpret_cast<double*>(p.nbr[d] + p.L.off_land[p.cur][dir_dx(d) < 0 ? 1 : 0]);
             xp.peer_flag[d] = reinterpret_cast<uint64_t*>(p.nbr[d] + kOffXchgFlags) + dir_opposite(d);
         }
     }
