@@ -100,7 +100,10 @@ struct LaunchParams {
 };
 
 __device__ __forceinline__ void decode_tile(int i, int nbx, int nby, int& tx, int& ty) {
-    // Boundary ring first, then interior strips with y fastest.
+    // Boundary ring first, then the interior with x fastest: tiles i+-1 (x
+    // neighbours) and i+-(nbx-2) (y neighbours) are all in flight within about
+    // one round of the persistent grid, so halo sectors are re-read from L2,
+    // not from DRAM (ncu: y-fastest order re-read 23 % of the grid from DRAM).
     if (nby == 1) { tx = i; ty = 0; return; }
     if (i < nbx) { tx = i; ty = 0; return; }
     i -= nbx;
@@ -113,8 +116,9 @@ __device__ __forceinline__ void decode_tile(int i, int nbx, int nby, int& tx, in
         if (i < mid) { tx = nbx - 1; ty = 1 + i; return; }
         i -= mid;
     }
-    tx = 1 + i / mid;
-    ty = 1 + i % mid;
+    const int midx = nbx - 2;
+    tx = 1 + i % midx;
+    ty = 1 + i / midx;
 }
 
 // Bit d set <=> the tile touches the tile edge facing direction d.

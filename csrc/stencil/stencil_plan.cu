@@ -316,9 +316,15 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         cuuint64_t gstr[1] = {(cuuint64_t)p.L.pitch * sizeof(double)};
         cuuint32_t box[2] = {(cuuint32_t)(kTileW + 2 * RA), (cuuint32_t)(kTileH + 2 * R)};
         cuuint32_t estr[2] = {1, 1};
+        const char* pe = std::getenv("B2C_STENCIL_L2PROMO");
+        const int promo = pe ? std::atoi(pe) : 128;
+        const CUtensorMapL2promotion l2p = promo >= 256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+                                         : promo >= 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                         : promo >= 64  ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                                        : CU_TENSOR_MAP_L2_PROMOTION_NONE;
         CUresult r = enc(&p.tmap[b], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, p.base + p.L.off_x[b], gdim,
                          gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                         l2p, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         B200_REQUIRE(r == CUDA_SUCCESS, ERR_CUDA,
                      "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
     }
