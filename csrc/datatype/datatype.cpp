@@ -241,6 +241,13 @@ bool Datatype::contiguous_layout() const {
     const Impl& t = need(impl_);
     return t.runs.size() == 1 && t.runs[0].disp == 0 && t.runs[0].len == t.extent;
 }
+bool Datatype::homogeneous(Basic* kind, int64_t* n) const {
+    const Impl& t = need(impl_);
+    if (t.sig.size() != 1) return false;
+    if (kind) *kind = (Basic)t.sig[0].kind;
+    if (n) *n = t.sig[0].rep;
+    return true;
+}
 uint64_t Datatype::signature_hash() const {
     const Impl& t = need(impl_);
     // hash of the size-class sequence (types of equal size are interchangeable

@@ -62,6 +62,103 @@ int b2c_ipc_close(void* ptr);
 int b2c_enable_peer_access(int device, int peer_device);
 int b2c_can_access_peer(int device, int peer_device, int* yes);
 
+/* -------------------------------------------------------------- datatypes */
+/* Derived datatypes.  Reference: MPI_Type_indexed (mpi7.cpp:32-41),
+ * MPI_Type_create_struct + MPI_Type_extent (mpi8.cpp:38-54),
+ * MPI_Type_create_subarray (mpi-complex-types.cpp:33-36, stencil2d/stencil2D.h:210-228),
+ * MPI_Type_create_hindexed (mpi-complex-types.cpp:38-50), commit/free.
+ * basic kinds: 0 BYTE 1 CHAR 2 INT8 3 UINT8 4 INT16 5 INT32 6 INT64 7 UINT64
+ *              8 FLOAT 9 DOUBLE 10 UINT32                                    */
+typedef struct b2c_type b2c_type;
+int b2c_type_basic(int kind, b2c_type** out);
+int b2c_type_contiguous(int count, b2c_type* old, b2c_type** out);
+int b2c_type_vector(int count, int blocklen, int stride, b2c_type* old, b2c_type** out);
+int b2c_type_hvector(int count, int blocklen, int64_t stride_bytes, b2c_type* old, b2c_type** out);
+int b2c_type_indexed(int n, const int* blocklens, const int* disps, b2c_type* old, b2c_type** out);
+int b2c_type_hindexed(int n, const int* blocklens, const int64_t* byte_disps, b2c_type* old,
+                      b2c_type** out);
+int b2c_type_struct(int n, const int* blocklens, const int64_t* byte_disps, b2c_type* const* types,
+                    b2c_type** out);
+int b2c_type_subarray(int ndims, const int* sizes, const int* subsizes, const int* starts,
+                      int order /*0 C, 1 Fortran*/, b2c_type* old, b2c_type** out);
+int b2c_type_resized(b2c_type* old, int64_t lb, int64_t extent, b2c_type** out);
+int b2c_type_commit(b2c_type* t);
+int b2c_type_free(b2c_type* t);
+int b2c_type_size(b2c_type* t, int64_t* size);
+int b2c_type_extent(b2c_type* t, int64_t* lb, int64_t* extent);
+int b2c_type_runs(b2c_type* t, int64_t count, int64_t* disp_len_pairs, int64_t cap, int64_t* n);
+int b2c_type_pack(b2c_type* t, const void* buf, int64_t count, void* packed);
+int b2c_type_unpack(b2c_type* t, const void* packed, int64_t bytes, void* buf, int64_t count);
+int b2c_type_describe(b2c_type* t, char* buf, int cap);
+
+/* ------------------------------------------------------------ communication */
+/* MPI-like communicators over the built-in host transport (threads of one
+ * process, or processes attached to a POSIX shared-memory segment).
+ * Reference: MPI_Init/Finalize/Comm_rank/Comm_size/Get_processor_name/Wtime/
+ * Abort (mpi1.cpp:11-16, mpierr.h:41), Send/Recv/Probe/Get_count (mpi3.cpp:26-46),
+ * Isend/Irecv/Wait/Waitall (mpi5.cpp:34-75), Gather/Bcast/Reduce/Allreduce
+ * (mpi6.cpp:89-100, mpi9.cpp:51-54, mpicuda2.cu:154,293), groups (mpi9.cpp:26-54),
+ * Cartesian topology (mpi10.cpp:22-54).                                       */
+#define B2C_ANY_SOURCE (-1)
+#define B2C_ANY_TAG (-1)
+#define B2C_PROC_NULL (-2)
+#define B2C_UNDEFINED (-32766)
+typedef struct b2c_comm b2c_comm;
+typedef struct b2c_request b2c_request;
+typedef struct { int source, tag, error; int64_t bytes; } b2c_status;
+/* reduction ops: 0 SUM 1 PROD 2 MAX 3 MIN 4 LAND 5 LOR 6 BAND 7 BOR */
+
+int b2c_init_local(int nranks, size_t ring_bytes, b2c_comm** out /* nranks handles */);
+int b2c_init_process(const char* job, int rank, int nranks, size_t ring_bytes, double timeout_s,
+                     b2c_comm** out);
+int b2c_init_env(b2c_comm** out);
+int b2c_comm_finalize(b2c_comm* c);
+int b2c_comm_free(b2c_comm* c);
+int b2c_comm_rank(b2c_comm* c, int* rank);
+int b2c_comm_size(b2c_comm* c, int* size);
+int b2c_comm_set_timeout(b2c_comm* c, double seconds);
+int b2c_abort(b2c_comm* c, int code);
+double b2c_wtime(void);
+int b2c_processor_name(char* buf, int cap);
+
+int b2c_send(b2c_comm* c, const void* buf, int64_t count, b2c_type* t, int dest, int tag);
+int b2c_recv(b2c_comm* c, void* buf, int64_t count, b2c_type* t, int src, int tag, b2c_status* st);
+int b2c_isend(b2c_comm* c, const void* buf, int64_t count, b2c_type* t, int dest, int tag,
+              b2c_request** out);
+int b2c_irecv(b2c_comm* c, void* buf, int64_t count, b2c_type* t, int src, int tag,
+              b2c_request** out);
+int b2c_wait(b2c_request* r, b2c_status* st);
+int b2c_test(b2c_request* r, int* flag, b2c_status* st);
+int b2c_waitall(int n, b2c_request** reqs, b2c_status* sts);
+int b2c_probe(b2c_comm* c, int src, int tag, b2c_status* st);
+int b2c_iprobe(b2c_comm* c, int src, int tag, int* flag, b2c_status* st);
+int b2c_get_count(const b2c_status* st, b2c_type* t, int64_t* count);
+int b2c_sendrecv(b2c_comm* c, const void* sbuf, int64_t scount, b2c_type* st, int dest, int stag,
+                 void* rbuf, int64_t rcount, b2c_type* rt, int src, int rtag, b2c_status* status);
+
+int b2c_barrier(b2c_comm* c);
+int b2c_bcast(b2c_comm* c, void* buf, int64_t count, b2c_type* t, int root);
+int b2c_reduce(b2c_comm* c, const void* sbuf, void* rbuf, int64_t count, b2c_type* t, int op, int root);
+int b2c_allreduce(b2c_comm* c, const void* sbuf, void* rbuf, int64_t count, b2c_type* t, int op);
+int b2c_gather(b2c_comm* c, const void* sbuf, int64_t scount, b2c_type* st, void* rbuf,
+               int64_t rcount, b2c_type* rt, int root);
+int b2c_scatter(b2c_comm* c, const void* sbuf, int64_t scount, b2c_type* st, void* rbuf,
+                int64_t rcount, b2c_type* rt, int root);
+int b2c_allgather(b2c_comm* c, const void* sbuf, int64_t scount, b2c_type* st, void* rbuf,
+                  int64_t rcount, b2c_type* rt);
+
+int b2c_comm_group(b2c_comm* c, int* world_ranks, int cap, int* n);
+int b2c_comm_create(b2c_comm* c, int n, const int* ranks_in_parent, b2c_comm** out);
+int b2c_comm_split(b2c_comm* c, int color, int key, b2c_comm** out);
+int b2c_comm_dup(b2c_comm* c, b2c_comm** out);
+int b2c_cart_create(b2c_comm* c, int ndims, const int* dims, const int* periods, int reorder,
+                    b2c_comm** out);
+int b2c_cart_coords(b2c_comm* c, int rank, int maxdims, int* coords);
+int b2c_cart_rank(b2c_comm* c, int ndims, const int* coords, int* rank);
+int b2c_cart_shift(b2c_comm* c, int dim, int disp, int* src, int* dst);
+int b2c_cart_get(b2c_comm* c, int maxdims, int* ndims, int* dims, int* periods);
+int b2c_dims_create(int nranks, int ndims, int* dims);
+
 /* ---------------------------------------------------------------- stencil */
 /* Fused 2-D stencil + halo exchange.  Reference capability: the exchange/
  * compute/terminate loop of stencil2d/mpi-2d-stencil-subarray-cuda.cu:169-172

@@ -62,6 +62,8 @@ public:
     const std::vector<Run>& runs() const;   // flat runs of ONE element
     uint64_t signature_hash() const;        // order-sensitive hash of the basic-type sequence
     bool contiguous_layout() const;         // one run at displacement 0 with len == extent
+    // true if one element is `n` values of a single basic kind (what reductions need)
+    bool homogeneous(Basic* kind, int64_t* n) const;
     std::string describe() const;
 
     // Runs of `count` consecutive elements (element i shifted by i * extent),
