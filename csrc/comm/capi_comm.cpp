@@ -8,13 +8,11 @@
 #include "b200comm/datatype.hpp"
 #include "comm/engine.hpp"
 #include "core/capi_util.hpp"
+#include "core/handles.hpp"
 
 using namespace b200;
 using namespace b200::comm;
 
-struct b2c_type { Datatype t; };
-struct b2c_comm { Comm c; };
-struct b2c_request { Request r; };
 
 static const Datatype& T(const b2c_type* t) {
     B200_REQUIRE(t != nullptr, ERR_TYPE, "null datatype handle");

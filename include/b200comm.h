@@ -159,6 +159,27 @@ int b2c_cart_shift(b2c_comm* c, int dim, int disp, int* src, int* dst);
 int b2c_cart_get(b2c_comm* c, int maxdims, int* ndims, int* dims, int* periods);
 int b2c_dims_create(int nranks, int ndims, int* dims);
 
+/* ---------------------------------------------------------- halo exchange */
+/* Layout descriptors, tile regions and the 8-neighbour halo plan with its
+ * UNFUSED exchange over the comm layer (any datatype, host or device tiles).
+ * Reference: stencil2d/stencil2D.h -- Array2D :30-42, RegionID :79-82,
+ * SubArrayRegion :107-201, CreateSendRecvArrays :381-437, ExchangeData :363-377,
+ * TestSubRegionExtraction :441-510.  C++ face: include/b200comm/stencil2d.hpp.
+ * regions: 0 TOP_LEFT 1 TOP_CENTER 2 TOP_RIGHT 3 CENTER_LEFT 4 CENTER
+ *          5 CENTER_RIGHT 6 BOTTOM_LEFT 7 BOTTOM_CENTER 8 BOTTOM_RIGHT
+ *          9 TOP 10 LEFT 11 BOTTOM 12 RIGHT                                  */
+typedef struct { int width, height, x_offset, y_offset, row_stride; } b2c_array2d;
+typedef struct b2c_halo_plan b2c_halo_plan;
+int b2c_sub_array_region(const b2c_array2d* g, int stencil_w, int stencil_h, int region,
+                         b2c_array2d* out);
+int b2c_halo_plan_create(b2c_comm* cart, const b2c_array2d* tile, int stencil_w, int stencil_h,
+                         b2c_type* elem, b2c_halo_plan** out);
+int b2c_halo_plan_destroy(b2c_halo_plan* p);
+int b2c_halo_exchange(b2c_halo_plan* p, void* tile_data);
+int b2c_halo_plan_entry(b2c_halo_plan* p, int which /*0 recv,1 send*/, int i, int* peer, int* tag,
+                        int* region, b2c_array2d* layout, int64_t* bytes);
+int b2c_region_report(int w, int h, int stencil_w, int stencil_h, char* buf, int cap);
+
 /* ---------------------------------------------------------------- stencil */
 /* Fused 2-D stencil + halo exchange.  Reference capability: the exchange/
  * compute/terminate loop of stencil2d/mpi-2d-stencil-subarray-cuda.cu:169-172

@@ -5,7 +5,7 @@ Multi-rank cases run as virtual ranks in one process, stepped in lock-step
 multi-process path, but never two kernels that wait on each other.
 """
 import os
-import re
+
 
 import pytest
 import torch
@@ -111,18 +111,19 @@ def test_residual_matches_oracle():
     assert grp.residual() == pytest.approx(want, rel=1e-11)
 
 
-@pytest.mark.skipif(not os.path.isdir(REF), reason="reference sample output not mounted")
-def test_exchange_reproduces_reference_golden_files():
+def test_exchange_reproduces_reference_golden_layout():
     """3x3 periodic grid, 16x16 tile, 5x5 stencil (ghost 2), core = rank id, ghosts = -1:
-    the tile after ONE exchange must equal stencil2d/sample-output/<r>_<c>."""
+    after ONE device-side exchange every ghost block holds the id of the neighbour on
+    that side -- the content of stencil2d/sample-output/<r>_<c> (compared with the
+    files themselves when the reference tree is mounted)."""
+    from test_halo_host import expected_tile
     grp = Stencil2D.create_group(cms.LocalGroup(9), (16, 16), 2, "star", dims=(3, 3), periods=True)
     for s in grp.ranks:
         s.fill(float(s.rank), -1.0)
     grp.exchange()
     for s in grp.ranks:
         r, c = s.cart.coords(s.rank)
-        text = open(f"{REF}/{r}_{c}").read()
-        golden = text.split("Array after exchange\n")[1]
-        assert s.dump_str() == golden, f"tile {r}_{c} differs from the reference dump"
-        before = re.search(r"\nArray\n(.*?)\n\n", text, re.S).group(1) + "\n"
-        assert before.count("\n") == 20
+        assert torch.equal(s.tile.cpu(), expected_tile(s.cart, s.rank, 16, 2))
+        if os.path.isdir(REF):
+            golden = open(f"{REF}/{r}_{c}").read().split("Array after exchange\n")[1]
+            assert s.dump_str() == golden, f"tile {r}_{c} differs from the reference dump"
