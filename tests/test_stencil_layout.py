@@ -13,7 +13,7 @@ def test_layout_alignment():
     assert L.pitch % 16 == 0 and L.pitch >= L.lead + L.W + 2
     assert L.rows == 16384 + 2
     assert L.off_buf0 % 1024 == 0 and L.off_buf1 % 1024 == 0
-    assert L.total_bytes == L.pad_bytes + 2 * L.tile_bytes
+    assert L.total_bytes >= L.pad_bytes + 2 * L.tile_bytes   # + 4 column landing buffers
 
 
 def test_layout_rejects_bad_shapes():
