@@ -1,0 +1,328 @@
+// Distributed dot product: local reduction fused with a one-shot P2P allreduce.
+//
+// Reference capability: mpicuda2.cu / mpicuda3.cu / mpicuda4.cu
+// -- per-rank kernel (atomicAdd variant :65-81, per-block partials :84-100,
+// single-launch "last block finishes" mpicuda4.cu:157-185), then D2H of the
+// scalar, then MPI_Reduce(SUM, root 0) on the host (mpicuda4.cu:354-368).
+//
+// Here ONE kernel per rank does everything:
+//   1. grid-stride FMA over 16-byte vector loads, fp64 accumulation;
+//   2. per-CTA partial -> scratch[blockIdx]; __threadfence; arrival counter;
+//   3. the LAST CTA sums the partials in a fixed order (deterministic), then
+//      -- instead of returning to the host -- stores the rank's partial into
+//      slot[my_rank] of EVERY peer's symmetric slot table (8-byte peer stores
+//      over NVLink) and release-stores the epoch next to it;
+//   4. the same CTA acquires the epochs of all ranks in its own table and adds
+//      the P values in rank order, so every rank gets bit-identical results.
+// No D2H, no host MPI, no second launch.  `phases` lets single-GPU emulation of
+// several ranks split push (bit 0) and gather (bit 1) into two launches, because
+// kernels that wait on each other must not be queued on one GPU.
+//
+// The reference's other two local-reduce variants (atomicAdd per block, host
+// finish of per-block partials) are kept in csrc/baseline/ as baselines.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <new>
+#include <string>
+
+#include "b200comm.h"
+#include "b200comm/error.hpp"
+#include "core/capi_util.hpp"
+#include "kernels/ptx.cuh"
+
+namespace b200 {
+namespace dot {
+
+constexpr int kThreads = 256;
+constexpr int kMaxRanks = 64;
+constexpr int kUnroll = 4;
+
+// One slot per (parity, source rank): {value, epoch}; 16 bytes.
+struct Slot {
+    double value;
+    uint64_t epoch;
+};
+
+struct Params {
+    const void* x;
+    const void* y;
+    int64_t n;
+    double* partials;          // scratch: [gridDim.x]
+    unsigned int* counter;     // scratch: arrival counter (self-resetting)
+    Slot* my_slots;            // [2][nranks] in my symmetric block
+    Slot* peer_slots[kMaxRanks];   // every rank's table (peer mapped), incl. mine
+    double* out;               // device scalar result
+    unsigned int* status;
+    uint64_t timeout_ns;
+    uint64_t epoch;            // 1, 2, 3, ... (same on every rank)
+    int rank, nranks;
+    int root;                  // -1: allreduce, else reduce to this rank
+    int phases;                // bit0 local reduce + push, bit1 gather + sum
+};
+
+template <typename T> struct Vec;
+template <> struct Vec<double> { using type = double2; static constexpr int N = 2; };
+template <> struct Vec<float> { using type = float4; static constexpr int N = 4; };
+
+__device__ __forceinline__ double dotv(const double2& a, const double2& b, double acc) {
+    acc = fma(a.x, b.x, acc);
+    return fma(a.y, b.y, acc);
+}
+__device__ __forceinline__ double dotv(const float4& a, const float4& b, double acc) {
+    acc = fma((double)a.x, (double)b.x, acc);
+    acc = fma((double)a.y, (double)b.y, acc);
+    acc = fma((double)a.z, (double)b.z, acc);
+    return fma((double)a.w, (double)b.w, acc);
+}
+
+__device__ __forceinline__ double block_sum(double v, double* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) sh[warp] = v;
+    __syncthreads();
+    double s = 0.0;
+    if (warp == 0) {
+        s = lane < (int)(blockDim.x >> 5) ? sh[lane] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    }
+    __syncthreads();
+    return s;   // valid in warp 0
+}
+
+// Steps 3 and 4 of the header comment, executed by one CTA.
+__device__ void exchange_and_finish(const Params& P, double local, double* sh) {
+    const int par = (int)(P.epoch & 1);
+    if (P.phases & 1) {
+        // push my partial to every rank that needs it (one 16-byte slot each)
+        for (int r = threadIdx.x; r < P.nranks; r += blockDim.x) {
+            if (P.root >= 0 && r != P.root) continue;
+            Slot* s = P.peer_slots[r] + (size_t)par * P.nranks + P.rank;
+            s->value = local;
+            ptx::st_release_sys(&s->epoch, P.epoch);
+        }
+    }
+    if (!(P.phases & 2)) return;
+    if (P.root >= 0 && P.rank != P.root) return;
+    // gather: thread r waits for rank r, then a fixed-order sum
+    double v = 0.0;
+    if ((int)threadIdx.x < P.nranks) {
+        const Slot* s = P.my_slots + (size_t)par * P.nranks + threadIdx.x;
+        const uint64_t t0 = ptx::globaltimer_ns();
+        uint32_t spins = 0;
+        while (ptx::ld_acquire_sys(&s->epoch) < P.epoch) {
+            if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
+                atomicOr(P.status, 2u);
+                break;
+            }
+        }
+        v = *reinterpret_cast<const volatile double*>(&s->value);
+    }
+    __shared__ double vals[kMaxRanks];
+    if ((int)threadIdx.x < P.nranks) vals[threadIdx.x] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int r = 0; r < P.nranks; ++r) tot += vals[r];   // rank order: same bits everywhere
+        *P.out = tot;
+    }
+    (void)sh;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 4) dot_fused_kernel(const __grid_constant__ Params P) {
+    using V = typename Vec<T>::type;
+    constexpr int VN = Vec<T>::N;
+    __shared__ double sh[kThreads / 32];
+    __shared__ bool last;
+    if (!(P.phases & 1)) {          // gather-only launch (emulation): one CTA
+        if (blockIdx.x == 0) exchange_and_finish(P, 0.0, sh);
+        return;
+    }
+    const T* x = static_cast<const T*>(P.x);
+    const T* y = static_cast<const T*>(P.y);
+    const int64_t nvec = P.n / VN;
+    const V* xv = reinterpret_cast<const V*>(x);
+    const V* yv = reinterpret_cast<const V*>(y);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double acc[kUnroll] = {0.0, 0.0, 0.0, 0.0};
+    // main loop: kUnroll independent 16-byte loads of each operand in flight
+    for (; i + (kUnroll - 1) * stride < nvec; i += kUnroll * stride) {
+        V a[kUnroll], b[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            a[u] = __ldcs(xv + i + u * stride);
+            b[u] = __ldcs(yv + i + u * stride);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) acc[u] = dotv(a[u], b[u], acc[u]);
+    }
+    for (; i < nvec; i += stride) acc[0] = dotv(__ldcs(xv + i), __ldcs(yv + i), acc[0]);
+    // scalar tail
+    for (int64_t k = nvec * VN + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < P.n; k += stride)
+        acc[0] = fma((double)x[k], (double)y[k], acc[0]);
+    double s = block_sum((acc[0] + acc[1]) + (acc[2] + acc[3]), sh);
+    if (threadIdx.x == 0) {
+        P.partials[blockIdx.x] = s;
+        __threadfence();
+        const unsigned int v = atomicInc(P.counter, gridDim.x - 1);   // wraps back to 0
+        last = v == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    // the last CTA: deterministic sum of the partials ...
+    double t = 0.0;
+    for (int k = threadIdx.x; k < (int)gridDim.x; k += blockDim.x)
+        t += *reinterpret_cast<volatile double*>(P.partials + k);
+    t = block_sum(t, sh);
+    __shared__ double local_total;
+    if (threadIdx.x == 0) local_total = t;
+    __syncthreads();
+    // ... and the cross-GPU exchange, in the same kernel
+    exchange_and_finish(P, local_total, sh);
+}
+
+struct Plan {
+    int device;
+    int rank, nranks;
+    int grid;
+    double* partials;
+    unsigned int* counter;
+    double* out;
+    unsigned int* status;
+    Slot* my_slots;
+    Slot* peer_slots[kMaxRanks];
+    uint64_t epoch;
+    uint64_t timeout_ns;
+    bool owns_scratch;
+};
+
+}  // namespace dot
+}  // namespace b200
+
+using namespace b200;
+using namespace b200::dot;
+
+struct b2c_dot { Plan p; };
+
+static void launch_dot(const Plan& pl, const void* x, const void* y, int64_t n, int dtype, int root,
+                       int phases, double* partials, unsigned int* counter, cudaStream_t st) {
+    Params P{};
+    P.x = x; P.y = y; P.n = n;
+    P.partials = partials; P.counter = counter;
+    P.my_slots = pl.my_slots;
+    for (int r = 0; r < pl.nranks; ++r) P.peer_slots[r] = pl.peer_slots[r];
+    P.out = pl.out; P.status = pl.status; P.timeout_ns = pl.timeout_ns;
+    P.epoch = pl.epoch; P.rank = pl.rank; P.nranks = pl.nranks; P.root = root; P.phases = phases;
+    const int grid = (phases & 1) ? pl.grid : 1;
+    if (dtype == 9) dot_fused_kernel<double><<<grid, kThreads, 0, st>>>(P);
+    else dot_fused_kernel<float><<<grid, kThreads, 0, st>>>(P);
+    B200_CHECK_LAUNCH();
+}
+
+extern "C" {
+
+// Bytes of symmetric memory a dot plan needs on every rank (slot tables).
+B2C_EXPORT int b2c_dot_symmetric_bytes(int nranks, size_t* bytes) {
+    B2C_TRY
+    B200_REQUIRE(bytes && nranks >= 1 && nranks <= kMaxRanks, ERR_ARG, "bad rank count");
+    *bytes = (((size_t)2 * nranks * sizeof(Slot)) + 255) & ~(size_t)255;
+    B2C_CATCH
+}
+
+// `slot_tables[r]` = address of rank r's slot table as mapped in THIS process
+// (slot_tables[rank] is the local one).  The tables must start zeroed.
+B2C_EXPORT int b2c_dot_create(b2c_dot** out, int rank, int nranks, void* const* slot_tables) {
+    B2C_TRY
+    B200_REQUIRE(out && slot_tables, ERR_ARG, "null argument");
+    B200_REQUIRE(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks, ERR_RANK,
+                 "bad rank / rank count");
+    auto* h = new (std::nothrow) b2c_dot();
+    B200_REQUIRE(h, ERR_NOMEM, "plan allocation failed");
+    Plan& p = h->p;
+    p = Plan{};
+    B200_CHECK_CUDA(cudaGetDevice(&p.device));
+    int sms = 0;
+    B200_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p.device));
+    p.rank = rank; p.nranks = nranks;
+    p.grid = sms * 4;     // 4 x 256 threads per SM, one wave, 128 B of loads in flight per thread
+    for (int r = 0; r < nranks; ++r) p.peer_slots[r] = static_cast<Slot*>(slot_tables[r]);
+    p.my_slots = p.peer_slots[rank];
+    // scratch: per-CTA partials, arrival counter, result, status
+    B200_CHECK_CUDA(cudaMalloc(&p.partials, (size_t)p.grid * sizeof(double)));
+    B200_CHECK_CUDA(cudaMalloc(&p.counter, 256));
+    B200_CHECK_CUDA(cudaMemset(p.counter, 0, 256));
+    p.out = reinterpret_cast<double*>(reinterpret_cast<char*>(p.counter) + 64);
+    p.status = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(p.counter) + 128);
+    p.epoch = 0;
+    p.timeout_ns = 20ull * 1000 * 1000 * 1000;
+    p.owns_scratch = true;
+    *out = h;
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_dot_destroy(b2c_dot* h) {
+    B2C_TRY
+    if (!h) return 0;
+    if (h->p.owns_scratch) { cudaFree(h->p.partials); cudaFree(h->p.counter); }
+    delete h;
+    B2C_CATCH
+}
+
+// Enqueue one fused dot + allreduce (root < 0) or dot + reduce-to-root.
+// dtype: 8 float32, 9 float64 (the basic-kind numbering of the datatype API).
+// phases: 3 = everything in one launch (one rank per GPU);
+//         1 then 2 = push and gather as separate launches (several emulated ranks on one GPU).
+// The epoch advances when bit 0 is set.
+B2C_EXPORT int b2c_dot_run(b2c_dot* h, const void* x, const void* y, int64_t n, int dtype, int root,
+                           int phases, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h && (x || n == 0) && (y || n == 0), ERR_ARG, "null argument");
+    B200_REQUIRE(dtype == 8 || dtype == 9, ERR_TYPE, "dot supports float32 and float64");
+    B200_REQUIRE(n >= 0, ERR_COUNT, "negative length");
+    B200_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, ERR_BUFFER,
+                 "dot operands must be 16-byte aligned");
+    B200_REQUIRE(root < h->p.nranks, ERR_RANK, "root out of range");
+    B200_REQUIRE((phases & 3) != 0, ERR_ARG, "phases must include push (1) and/or gather (2)");
+    Plan& p = h->p;
+    if (phases & 1) p.epoch += 1;
+    launch_dot(p, x, y, n, dtype, root, phases, p.partials, p.counter, (cudaStream_t)stream);
+    B2C_CATCH
+}
+
+// Device address of the result scalar (valid after the launch with bit 1 completed).
+B2C_EXPORT int b2c_dot_result_ptr(b2c_dot* h, double** out) {
+    B2C_TRY
+    B200_REQUIRE(h && out, ERR_ARG, "null argument");
+    *out = h->p.out;
+    B2C_CATCH
+}
+
+// Synchronises `stream`, returns the result and raises ERR_TIMEOUT if a peer never delivered.
+B2C_EXPORT int b2c_dot_result(b2c_dot* h, void* stream, double* value) {
+    B2C_TRY
+    B200_REQUIRE(h && value, ERR_ARG, "null argument");
+    struct { double v; char pad[56]; unsigned int st; } host{};
+    B200_CHECK_CUDA(cudaMemcpyAsync(&host.v, h->p.out, sizeof(double), cudaMemcpyDeviceToHost,
+                                    (cudaStream_t)stream));
+    B200_CHECK_CUDA(cudaMemcpyAsync(&host.st, h->p.status, sizeof(unsigned), cudaMemcpyDeviceToHost,
+                                    (cudaStream_t)stream));
+    B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    B200_REQUIRE((host.st & 2u) == 0, ERR_TIMEOUT,
+                 "dot allreduce: a peer's partial never arrived (device-side wait timed out)");
+    *value = host.v;
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_dot_set_timeout_ms(b2c_dot* h, unsigned long long ms) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    h->p.timeout_ns = ms * 1000000ull;
+    B2C_CATCH
+}
+
+}  // extern "C"

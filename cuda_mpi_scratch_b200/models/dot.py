@@ -1,0 +1,145 @@
+"""Distributed dot product with the cross-GPU reduction fused into the kernel.
+
+Capability parity with the reference's ``mpicuda2.cu`` / ``mpicuda3.cu`` /
+``mpicuda4.cu``: the global vectors are block-decomposed over the ranks
+(``ARRAY_SIZE / numtasks`` each, ``mpicuda2.cu:158-165``), every rank reduces its
+slice on its GPU and the partial results are summed (``MPI_Reduce`` to rank 0,
+``mpicuda2.cu:293``; all-ones inputs must give the element count, ``:296-298``).
+
+The reference copies the per-rank scalar to the host and calls MPI.  Here one
+kernel per rank does the local reduction *and* the allreduce: the last CTA
+stores the partial into every peer's slot table over NVLink and sums what the
+peers stored into its own (``csrc/kernels/dot.cu``).  ``baseline_dot`` runs the
+reference-style kernels + a host-side sum for comparison.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _lib
+from ..parallel.symmetric import SymmetricBuffer
+from ..parallel.world import LocalGroup, World
+
+_L = _lib.lib
+_vp, _i32, _i64 = C.c_void_p, C.c_int, C.c_int64
+_lib._proto("b2c_dot_symmetric_bytes", [_i32, C.POINTER(C.c_size_t)])
+_lib._proto("b2c_dot_create", [C.POINTER(_vp), _i32, _i32, C.POINTER(_vp)])
+_lib._proto("b2c_dot_destroy", [_vp])
+_lib._proto("b2c_dot_run", [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp])
+_lib._proto("b2c_dot_result_ptr", [_vp, C.POINTER(_vp)])
+_lib._proto("b2c_dot_result", [_vp, _vp, C.POINTER(C.c_double)])
+_lib._proto("b2c_dot_set_timeout_ms", [_vp, C.c_ulonglong])
+_lib._proto("b2c_baseline_dot_blocks", [_i64])
+_lib._proto("b2c_baseline_dot", [_i32, _vp, _vp, _i64, _i32, _vp, _vp])
+
+_DT = {torch.float32: 8, torch.float64: 9}
+
+
+def _stream(device: int) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def symmetric_bytes(nranks: int) -> int:
+    n = C.c_size_t()
+    _lib.check(_L.b2c_dot_symmetric_bytes(nranks, C.byref(n)))
+    return n.value
+
+
+class DistributedDot:
+    """One rank's plan.  ``create`` (one rank per process) or ``create_group``
+    (virtual ranks in one process)."""
+
+    def __init__(self, rank: int, nranks: int, symbuf: SymmetricBuffer, world: World | None):
+        self.rank, self.nranks, self.symbuf, self.world = rank, nranks, symbuf, world
+        self.device = symbuf.device
+        tables = (C.c_void_p * nranks)(*[symbuf.peer_ptr(r) for r in range(nranks)])
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_dot_create(C.byref(h), rank, nranks, tables))
+        self._h = h
+        self.kernel_launches = 0
+
+    @classmethod
+    def create(cls, world: World) -> "DistributedDot":
+        sym = SymmetricBuffer.allocate(world, symmetric_bytes(world.size))
+        return cls(world.rank, world.size, sym, world)
+
+    @classmethod
+    def create_group(cls, group: LocalGroup) -> "DotGroup":
+        syms = SymmetricBuffer.allocate_local(group, symmetric_bytes(group.size))
+        return DotGroup([cls(r, group.size, syms[r], None) for r in range(group.size)])
+
+    def launch(self, x: torch.Tensor, y: torch.Tensor, root: int | None = None,
+               phases: int = 3) -> None:
+        """Enqueue the fused kernel on the current stream (no host sync)."""
+        if x.dtype != y.dtype or x.dtype not in _DT:
+            raise TypeError("dot needs two float32 or two float64 tensors")
+        if x.numel() != y.numel() or not (x.is_contiguous() and y.is_contiguous()):
+            raise ValueError("dot needs contiguous tensors of equal length")
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_dot_run(self._h, x.data_ptr(), y.data_ptr(), x.numel(), _DT[x.dtype],
+                                      -1 if root is None else root, phases, _stream(self.device)))
+        self.kernel_launches += 1
+
+    def result(self) -> float:
+        """Synchronise the stream and return the reduced value."""
+        v = C.c_double()
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_dot_result(self._h, _stream(self.device), C.byref(v)))
+        return v.value
+
+    def result_tensor(self) -> torch.Tensor:
+        """The device scalar the kernel writes (no synchronisation)."""
+        from ..parallel.symmetric import as_tensor
+        p = C.c_void_p()
+        _lib.check(_L.b2c_dot_result_ptr(self._h, C.byref(p)))
+        return as_tensor(p.value, (1,), torch.float64, self.device, owner=self)
+
+    def dot(self, x: torch.Tensor, y: torch.Tensor, root: int | None = None) -> float:
+        """``sum_over_ranks(x_r . y_r)`` -- on every rank (``root=None``) or on ``root``."""
+        self.launch(x, y, root)
+        return self.result()
+
+    def close(self) -> None:
+        if self._h:
+            _L.b2c_dot_destroy(self._h)
+            self._h = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DotGroup:
+    """Virtual ranks of one process: push phase for all ranks, then gather phase
+    (two launches per rank, never a kernel waiting for an unlaunched one)."""
+
+    def __init__(self, ranks: list[DistributedDot]):
+        self.ranks = ranks
+
+    def dot(self, xs: list[torch.Tensor], ys: list[torch.Tensor], root: int | None = None) -> list[float]:
+        for d, x, y in zip(self.ranks, xs, ys):
+            d.launch(x, y, root, phases=1)
+        for dev in {d.device for d in self.ranks}:
+            torch.cuda.synchronize(dev)
+        for d in self.ranks:
+            if root is None or d.rank == root:
+                d.launch(xs[d.rank][:0], ys[d.rank][:0], root, phases=2)
+        return [d.result() if (root is None or d.rank == root) else float("nan") for d in self.ranks]
+
+
+def baseline_dot(x: torch.Tensor, y: torch.Tensor, variant: int = 2) -> float:
+    """Reference-style LOCAL dot (kernel variants of ``mpicuda2.cu`` / ``mpicuda4.cu``)
+    + D2H of the scalar (variant 1: of all per-block partials, summed on the host)."""
+    n = x.numel()
+    blocks = _L.b2c_baseline_dot_blocks(n)
+    out = torch.zeros(blocks, dtype=x.dtype, device=x.device)
+    _lib.check(_L.b2c_baseline_dot(variant, x.data_ptr(), y.data_ptr(), n, _DT[x.dtype],
+                                   out.data_ptr(), _stream(x.device.index)))
+    if variant == 1:
+        return float(out.cpu().sum())
+    return float(out[0].item())

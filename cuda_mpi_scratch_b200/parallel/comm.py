@@ -139,6 +139,14 @@ def _bufinfo(buf, count=None, datatype: Datatype | None = None):
     return addr, count, dt, keep
 
 
+def _sync_if_cuda(buf) -> None:
+    """A CUDA tensor is handed to the transport by ADDRESS: whatever produces it on
+    the current torch stream must be complete first (the rule of CUDA-aware MPI)."""
+    if getattr(buf, "is_cuda", False):
+        import torch
+        torch.cuda.current_stream(buf.device).synchronize()
+
+
 class Request:
     """``MPI_Request``; keeps the buffer alive until completion."""
 
@@ -185,6 +193,7 @@ class Comm:
     # ---- point to point ------------------------------------------------------
     def send(self, buf, dest: int, tag: int = 0, count=None, datatype=None) -> None:
         a, n, dt, keep = _bufinfo(buf, count, datatype)
+        _sync_if_cuda(buf)
         _lib.check(_L.b2c_send(self._h, a, n, dt._h, dest, tag))
 
     def recv(self, buf, source: int = ANY_SOURCE, tag: int = ANY_TAG, count=None,
@@ -197,6 +206,7 @@ class Comm:
 
     def isend(self, buf, dest: int, tag: int = 0, count=None, datatype=None) -> Request:
         a, n, dt, keep = _bufinfo(buf, count, datatype)
+        _sync_if_cuda(buf)
         h = C.c_void_p()
         _lib.check(_L.b2c_isend(self._h, a, n, dt._h, dest, tag, C.byref(h)))
         return Request(h.value, (keep, dt))

@@ -224,6 +224,56 @@ int b2c_stencil_exchange_wait(b2c_stencil* s, void* stream);
 int b2c_stencil_fill(b2c_stencil* s, int which, int region, double value, void* stream);
 int b2c_stencil_status(b2c_stencil* s, void* stream, unsigned int* status);
 
+/* ------------------------------------------------- P2P copy engine / flags */
+/* Kernel-initiated put into a peer-mapped buffer + device-side epoch flags, and a
+ * device-resident ping-pong loop.  Reference capability: the GPU ping-pong
+ * benchmarks test-benchmark/mpi-pingpong-gpu.cpp:24-83 (blocking) and
+ * mpi-pingpong-gpu-async.cpp:43-106 (Isend/Irecv/Wait, host-staged variants). */
+int b2c_p2p_put(void* dst_peer, const void* src, size_t bytes, void* peer_flag,
+                unsigned long long flag_value, void* counter, int mode /*0 LD/ST, 1 TMA*/,
+                int max_ctas, void* stream);
+int b2c_flag_wait(const void* flag, unsigned long long value, void* status,
+                  unsigned long long timeout_ms, void* stream);
+int b2c_flag_set(void* flag, unsigned long long value, void* stream);
+int b2c_pingpong_device(int role, int iters, size_t bytes, const void* send_local, void* recv_peer,
+                        const void* my_flag, void* peer_flag, unsigned long long base_epoch,
+                        double* out_ns, void* status, unsigned long long timeout_ms, void* stream);
+
+/* ------------------------------------------------ datatype-driven device moves */
+/* Pack + move + unpack in one kernel; src and dst may be peer mapped.  Reference
+ * capability: derived datatypes on device pointers handed to a CUDA-aware MPI
+ * (stencil2d/stencil2D.h:369-373); see also b2c_send/b2c_recv, which accept
+ * device buffers and use these kernels on the receiver side.                   */
+int b2c_typed_move(const void* src, b2c_type* stype, int64_t scount, void* dst, b2c_type* dtype,
+                   int64_t dcount, void* stream, int64_t* moved_bytes);
+int b2c_move_uniform(const void* src, void* dst, int64_t nruns, int64_t len, int64_t sstride,
+                     int64_t dstride, void* stream);
+int b2c_move_segments(const void* src, void* dst, const void* dev_segments, int64_t nseg,
+                      int64_t max_len, int64_t items_64k, void* stream);
+
+/* -------------------------------------------------------- distributed dot */
+/* Dot product whose local reduction is fused with a one-shot P2P allreduce
+ * (or reduce-to-root) in ONE kernel per rank.  Reference capability:
+ * mpicuda2.cu:65-100,259-293, mpicuda3.cu, mpicuda4.cu:97-185,347-368
+ * (kernel + D2H + MPI_Reduce on the host).                                   */
+typedef struct b2c_dot b2c_dot;
+int b2c_dot_symmetric_bytes(int nranks, size_t* bytes);
+int b2c_dot_create(b2c_dot** out, int rank, int nranks, void* const* slot_tables);
+int b2c_dot_destroy(b2c_dot* d);
+/* dtype 8 = float32, 9 = float64; root < 0 = allreduce; phases 3 = one launch */
+int b2c_dot_run(b2c_dot* d, const void* x, const void* y, int64_t n, int dtype, int root,
+                int phases, void* stream);
+int b2c_dot_result_ptr(b2c_dot* d, double** device_scalar);
+int b2c_dot_result(b2c_dot* d, void* stream, double* value);
+int b2c_dot_set_timeout_ms(b2c_dot* d, unsigned long long ms);
+
+/* Reference-STYLE local dot kernels, baselines only (csrc/baseline/):
+ * variant 0 atomicAdd per block (mpicuda2.cu:65-81), 1 per-block partials for a
+ * host finish (mpicuda2.cu:84-100), 2 last-block finish (mpicuda4.cu:157-185). */
+int b2c_baseline_dot_blocks(int64_t n);
+int b2c_baseline_dot(int variant, const void* a, const void* b, int64_t n, int dtype, void* out,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif
