@@ -1,1 +1,1 @@
-"""parallel subpackage."""
+"""Worlds, symmetric memory, Cartesian topology, MPI-like comm, datatypes, halo plans."""

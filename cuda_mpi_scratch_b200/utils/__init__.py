@@ -1,1 +1,1 @@
-"""utils subpackage."""
+"""Timing, clock sampling."""
