@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -322,6 +323,138 @@ B2C_EXPORT int b2c_dot_set_timeout_ms(b2c_dot* h, unsigned long long ms) {
     B2C_TRY
     B200_REQUIRE(h, ERR_ARG, "null plan");
     h->p.timeout_ns = ms * 1000000ull;
+    B2C_CATCH
+}
+
+}  // extern "C"
+
+// =============================================================================
+// Local dot product for callers that must not allocate
+// =============================================================================
+//
+// b2c_dot_create() above cudaMalloc's the kernel's scratch (per-CTA partial sums,
+// arrival counter, slot table).  Some users of this library cannot do that at
+// the place where they need a dot product:
+//   * a solver step that runs inside another runtime's callback or a latency-
+//     critical loop, where cudaMalloc is off limits because it synchronises the
+//     whole device and stalls every other stream;
+//   * a process whose GPU memory has been handed, in full, to a framework's
+//     caching allocator or to a fixed arena -- a driver-level allocation can then
+//     simply fail, or break the footprint the application promised its host;
+//   * code that is only given raw device pointers and a stream, with no place to
+//     keep a plan object alive between calls.
+// For them the same kernel is offered with its scratch in a fixed device array
+// that is part of the library image.  Every GPU on which the library is loaded
+// carries these kNoAllocBytes (8448 bytes) until the process exits.
+//
+// Rules that follow from sharing one array:
+//   * it keeps whatever the previous call left in it, so each call first clears
+//     the control words that must start at zero (arrival counter, slot epochs,
+//     status) with a stream-ordered memset; the partial sums are fully
+//     overwritten and need no clearing;
+//   * two calls whose execution overlaps on the same GPU (different streams, or
+//     different host threads) use the same scratch at the same time and corrupt
+//     each other's result -- serialise them on one stream;
+//   * the grid is limited to what the array can hold (kNoAllocMaxCtas partial
+//     sums); a request beyond that is rejected, never silently shrunk.
+//
+// The address of the array is looked up once per device, by the first call made
+// while that device is current (cudaGetSymbolAddress; its return code is
+// checked).  That first call does more than launch work, so make it before any
+// stream capture is started.
+namespace b200 {
+namespace dot {
+
+constexpr int kNoAllocMaxCtas = 1024;                 // partial sums the scratch can hold
+constexpr size_t kNoAllocCtrlBytes = 256;             // counter @0, status @64, slots @128
+constexpr size_t kNoAllocBytes = kNoAllocCtrlBytes + (size_t)kNoAllocMaxCtas * sizeof(double);  // 8448
+
+// File-scope device scratch.  In HOST code this name is only a handle for the
+// symbol, not an address a kernel could use; the device address comes from
+// cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+struct NoAllocDevice {
+    unsigned char* scratch = nullptr;   // device address of g_noalloc_scratch on this GPU
+    int sms = 0;
+};
+static NoAllocDevice g_noalloc_dev[64];
+static std::mutex g_noalloc_mu;
+
+// One-time set-up for the CURRENT device: resolve the scratch address.
+static const NoAllocDevice& noalloc_device() {
+    int dev = 0;
+    B200_CHECK_CUDA(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < 64, ERR_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    NoAllocDevice& d = g_noalloc_dev[dev];
+    if (d.scratch == nullptr) {
+        void* p = nullptr;
+        cudaError_t st = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (st != cudaSuccess || p == nullptr)
+            fail_cuda((int)st, "cudaGetSymbolAddress(g_noalloc_scratch)", __FILE__, __LINE__,
+                      "cannot resolve the built-in dot scratch on this device:");
+        int sms = 0;
+        B200_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        d.sms = sms;
+        d.scratch = static_cast<unsigned char*>(p);
+    }
+    return d;
+}
+
+}  // namespace dot
+}  // namespace b200
+
+extern "C" {
+
+B2C_EXPORT int b2c_dot_local_noalloc_limits(int* max_ctas, size_t* scratch_bytes) {
+    if (max_ctas) *max_ctas = kNoAllocMaxCtas;
+    if (scratch_bytes) *scratch_bytes = kNoAllocBytes;
+    return 0;
+}
+
+// result[0] = sum_i x[i] * y[i] for this GPU's vectors, computed by the fused dot
+// kernel with the library's built-in scratch: no cudaMalloc, no cudaFree, no plan.
+//   x, y    device vectors of n elements, 16-byte aligned (dtype 8 float32, 9 float64)
+//   ctas    thread blocks to use; 0 = 4 per SM.  More than the scratch can hold
+//           (b2c_dot_local_noalloc_limits) is an error.
+//   result  device address of one double, written by the kernel
+//   stream  the launch and the clearing memset are ordered on it; the caller
+//           synchronises before reading `result`
+// See the comment block above for the sharing rules (calls that overlap on a GPU
+// race) and for the first-call set-up.
+B2C_EXPORT int b2c_dot_local_noalloc(const void* x, const void* y, int64_t n, int dtype, int ctas,
+                                     double* result, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(result != nullptr, ERR_BUFFER, "null result pointer");
+    B200_REQUIRE((x && y) || n == 0, ERR_BUFFER, "null input vector");
+    B200_REQUIRE(dtype == 8 || dtype == 9, ERR_TYPE, "dot supports float32 (8) and float64 (9)");
+    B200_REQUIRE(n >= 0, ERR_COUNT, "negative length");
+    B200_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, ERR_BUFFER,
+                 "dot operands must be 16-byte aligned");
+    B200_REQUIRE(ctas >= 0, ERR_ARG, "negative block count");
+    const NoAllocDevice& d = noalloc_device();
+    const int grid = ctas > 0 ? ctas : d.sms * 4;
+    B200_REQUIRE(grid <= kNoAllocMaxCtas, ERR_ARG,
+                 "requested " + std::to_string(grid) + " thread blocks but the built-in scratch holds "
+                 "partial sums for at most " + std::to_string(kNoAllocMaxCtas) +
+                 "; pass a smaller `ctas` or use b2c_dot_create(), which sizes its own scratch");
+    cudaStream_t st = (cudaStream_t)stream;
+    // what must start at zero: arrival counter, status word, slot epochs
+    B200_CHECK_CUDA(cudaMemsetAsync(d.scratch, 0, kNoAllocCtrlBytes, st));
+    Params P{};
+    P.x = x; P.y = y; P.n = n;
+    P.counter = reinterpret_cast<unsigned int*>(d.scratch);
+    P.status = reinterpret_cast<unsigned int*>(d.scratch + 64);
+    P.my_slots = reinterpret_cast<Slot*>(d.scratch + 128);      // [2 parities][1 rank]
+    P.peer_slots[0] = P.my_slots;
+    P.partials = reinterpret_cast<double*>(d.scratch + kNoAllocCtrlBytes);
+    P.out = result;
+    P.timeout_ns = 1000ull * 1000 * 1000;
+    P.epoch = 1; P.rank = 0; P.nranks = 1; P.root = -1; P.phases = 3;
+    if (dtype == 9) dot_fused_kernel<double><<<grid, kThreads, 0, st>>>(P);
+    else dot_fused_kernel<float><<<grid, kThreads, 0, st>>>(P);
+    B200_CHECK_LAUNCH();
     B2C_CATCH
 }
 

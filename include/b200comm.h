@@ -267,6 +267,22 @@ int b2c_dot_result_ptr(b2c_dot* d, double** device_scalar);
 int b2c_dot_result(b2c_dot* d, void* stream, double* value);
 int b2c_dot_set_timeout_ms(b2c_dot* d, unsigned long long ms);
 
+/* Local dot product that allocates NOTHING (no counterpart in the reference).
+ * For callers that may not call cudaMalloc where they need the result: code
+ * inside another runtime's callback or a latency-critical loop (cudaMalloc
+ * synchronises the device), or a process whose GPU memory already belongs to a
+ * framework allocator / fixed arena.  The kernel's scratch is a fixed array
+ * inside the library image (8448 bytes per GPU, held until exit), so:
+ *   - at most 1024 thread blocks (b2c_dot_local_noalloc_limits); more is an error;
+ *   - all calls share that scratch: calls that overlap on one GPU race -- keep
+ *     them on one stream;
+ *   - the first call on a device also resolves the scratch address; make that
+ *     call before starting any stream capture.
+ * result is a device pointer to one double; synchronise `stream` before reading. */
+int b2c_dot_local_noalloc_limits(int* max_ctas, size_t* scratch_bytes);
+int b2c_dot_local_noalloc(const void* x, const void* y, int64_t n, int dtype /*8 f32, 9 f64*/,
+                          int ctas /*0 = 4 per SM*/, double* result, void* stream);
+
 /* Reference-STYLE local dot kernels, baselines only (csrc/baseline/):
  * variant 0 atomicAdd per block (mpicuda2.cu:65-81), 1 per-block partials for a
  * host finish (mpicuda2.cu:84-100), 2 last-block finish (mpicuda4.cu:157-185). */
