@@ -90,7 +90,13 @@ def main() -> int:
             world.barrier()
             return world.allreduce_max(e0.elapsed_time(e1) / a.iters * 1e3)
 
-        for name, fn in (("typed_move (ours, 1 kernel)", ours), ("pack + nccl + unpack", pack_nccl),
+        def ours_pull():
+            # receiver-driven: gather the PEER's columns by its type, scatter into my ghost strip
+            typed_move(sym.peer_ptr(peer), send_t, tile, recv_t, device=dev)
+
+        for name, fn in (("typed_move push (ours, 1 kernel)", ours),
+                         ("typed_move pull (ours, 1 kernel)", ours_pull),
+                         ("pack + nccl + unpack", pack_nccl),
                          ("contiguous copy of the same payload", contiguous)):
             us = timed(fn)
             if rank == 0:

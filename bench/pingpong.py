@@ -47,6 +47,7 @@ def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-bytes", type=int, default=1 << 30)
     ap.add_argument("--json", default="")
+    ap.add_argument("--ctas", type=int, default=0, help="CTAs of the put kernel (0 = library default)")
     ap.add_argument("--paths", default="kernel_ldst,kernel_tma,device_loop,copy_engine,nccl,"
                                        "comm_sync,comm_async,host_staged,host_staged_pinned")
     a = ap.parse_args()
@@ -72,11 +73,11 @@ def main() -> int:
 
         def roundtrip_kernel(mode):
             if rank == 0:
-                ch.put(peer, src, mode=mode)
+                ch.put(peer, src, mode=mode, max_ctas=a.ctas)
                 ch.wait(peer)
             else:
                 ch.wait(peer)
-                ch.put(peer, ch.recv_view(torch.float64, n), mode=mode)
+                ch.put(peer, ch.recv_view(torch.float64, n), mode=mode, max_ctas=a.ctas)
 
         def roundtrip_copy_engine():
             pdata = ch.symbuf.peer_ptr(peer) + _OFF_DATA
@@ -172,7 +173,7 @@ def main() -> int:
             rtt_max = world.allreduce_max(rtt_us) if path == "device_loop" else rtt_us
             if rank == 0:
                 rec = {"path": path, "bytes": nbytes, "iters": it, "rtt_us": round(rtt_max, 3),
-                       "GBps_per_direction": round(2 * nbytes / (rtt_max * 1e-6) / 2 / 1e9, 3),
+                       "GBps_one_way": round(nbytes / (rtt_max * 1e-6 / 2) / 1e9, 3),
                        "check": "PASSED" if ok else "FAILED", "timer": timer}
                 results.append(rec)
                 print(json.dumps(rec), flush=True)

@@ -19,6 +19,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <tuple>
 #include <vector>
 
 #include "b200comm.h"
@@ -167,11 +168,37 @@ static const MovePlan& get_plan(const std::vector<Run>& s, const std::vector<Run
     return cache.emplace(std::make_pair(key, device), p).first->second;
 }
 
+static int64_t run_plan(const MovePlan& p, const void* src, void* dst, cudaStream_t st);
+
+// Variant for callers that already hold a stable identity for the (src, dst)
+// run lists: the plan is looked up by that identity, no hashing of the runs.
+int64_t typed_move_cached(const void* src, const std::vector<Run>& sruns, void* dst,
+                          const std::vector<Run>& druns, const void* identity, cudaStream_t st) {
+    static std::map<const void*, MovePlan> by_id;
+    const MovePlan* p;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto it = by_id.find(identity);
+        p = it == by_id.end() ? nullptr : &it->second;
+    }
+    if (!p) {
+        int dev = 0;
+        B200_CHECK_CUDA(cudaGetDevice(&dev));
+        const MovePlan& built = get_plan(sruns, druns, dev);
+        std::lock_guard<std::mutex> lk(g_mu);
+        p = &by_id.emplace(identity, built).first->second;
+    }
+    return run_plan(*p, src, dst, st);
+}
+
 int64_t typed_move(const void* src, const std::vector<Run>& sruns, void* dst,
                    const std::vector<Run>& druns, cudaStream_t st) {
     int dev = 0;
     B200_CHECK_CUDA(cudaGetDevice(&dev));
-    const MovePlan& p = get_plan(sruns, druns, dev);
+    return run_plan(get_plan(sruns, druns, dev), src, dst, st);
+}
+
+static int64_t run_plan(const MovePlan& p, const void* src, void* dst, cudaStream_t st) {
     if (p.uniform) {
         packmove::launch_uniform(static_cast<const char*>(src) + p.s0, static_cast<char*>(dst) + p.d0,
                                  p.nruns, p.len, p.sstride, p.dstride, st);
@@ -305,8 +332,31 @@ B2C_EXPORT int b2c_typed_move(const void* src, b2c_type* stype, int64_t scount, 
     B2C_TRY
     B200_REQUIRE(src && dst && stype && dtype, ERR_ARG, "null argument");
     B200_REQUIRE(stype->t.committed() && dtype->t.committed(), ERR_TYPE, "datatype not committed");
-    const int64_t n = devp2p::typed_move(src, stype->t.flatten(scount), dst, dtype->t.flatten(dcount),
-                                         (cudaStream_t)stream);
+    // Flattening + intersecting the run lists is host work proportional to the
+    // number of runs (4096 for one ghost column of a 4096^2 tile): do it once per
+    // (types, counts, device) and keep the committed types alive with the entry.
+    struct Key {
+        const void* s; const void* d; int64_t sc, dc; int dev;
+        bool operator<(const Key& o) const {
+            return std::tie(s, d, sc, dc, dev) < std::tie(o.s, o.d, o.sc, o.dc, o.dev);
+        }
+    };
+    struct Entry { Datatype st, dt; std::vector<Run> sruns, druns; };
+    static std::map<Key, Entry> cache;
+    static std::mutex mu;
+    int dev = 0;
+    B200_CHECK_CUDA(cudaGetDevice(&dev));
+    const Entry* e;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        Key k{stype->t.id(), dtype->t.id(), scount, dcount, dev};
+        auto it = cache.find(k);
+        if (it == cache.end())
+            it = cache.emplace(k, Entry{stype->t, dtype->t, stype->t.flatten(scount),
+                                        dtype->t.flatten(dcount)}).first;
+        e = &it->second;
+    }
+    const int64_t n = devp2p::typed_move_cached(src, e->sruns, dst, e->druns, e, (cudaStream_t)stream);
     if (moved) *moved = n;
     B2C_CATCH
 }

@@ -50,10 +50,7 @@ __device__ __forceinline__ void publish_when_last(const PutParams& P) {
         last = atomicInc(P.counter, gridDim.x - 1) == gridDim.x - 1;
     }
     __syncthreads();
-    if (last && threadIdx.x == 0 && P.peer_flag) {
-        ptx::fence_acq_rel_sys();
-        ptx::st_release_sys(P.peer_flag, P.flag_value);
-    }
+    if (last && threadIdx.x == 0 && P.peer_flag) ptx::st_release_sys(P.peer_flag, P.flag_value);
 }
 
 __global__ void __launch_bounds__(kThreads) put_ldst_kernel(const __grid_constant__ PutParams P) {
@@ -197,10 +194,7 @@ __global__ void __launch_bounds__(1024) pingpong_kernel(const __grid_constant__ 
                 P.recv_peer[b] = *reinterpret_cast<const volatile char*>(P.send_local + b);
         }
         __syncthreads();
-        if (threadIdx.x == 0) {
-            ptx::fence_acq_rel_sys();
-            ptx::st_release_sys(P.peer_flag, epoch);
-        }
+        if (threadIdx.x == 0) ptx::st_release_sys(P.peer_flag, epoch);   // release is cumulative over the barrier
         if (P.role == 0) {   // initiator waits for the echo
             if (threadIdx.x == 0) {
                 uint32_t spins = 0;

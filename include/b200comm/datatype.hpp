@@ -77,6 +77,7 @@ public:
     void unpack(const void* packed, int64_t packed_bytes, void* buf, int64_t count) const;
 
     bool operator==(const Datatype& o) const { return impl_ == o.impl_; }
+    const void* id() const { return impl_.get(); }   // identity of the underlying type
 
     struct Impl;
 private:
