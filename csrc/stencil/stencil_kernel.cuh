@@ -202,8 +202,14 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                 }
                 ptx::mbar_wait(&empty[stage], phase ^ 1u);
                 ptx::mbar_arrive_expect_tx(&full[stage], G::BOX_BYTES);
-                ptx::tma_load_2d(smem + stage * G::STAGE_BYTES, &tmap_in,
-                                 P.lead + tx * kTileW - G::RA, ty * kTileH + P.g - R, &full[stage]);
+                if (P.debug & 8)
+                    ptx::tma_load_2d_hint(smem + stage * G::STAGE_BYTES, &tmap_in,
+                                          P.lead + tx * kTileW - G::RA, ty * kTileH + P.g - R,
+                                          &full[stage], (P.debug & 16) ? ptx::l2_policy_evict_last()
+                                                                       : ptx::l2_policy_evict_first());
+                else
+                    ptx::tma_load_2d(smem + stage * G::STAGE_BYTES, &tmap_in,
+                                     P.lead + tx * kTileW - G::RA, ty * kTileH + P.g - R, &full[stage]);
                 if (++stage == NSTAGES) { stage = 0; phase ^= 1u; }
             }
         }
@@ -346,7 +352,8 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                 const int gy = ty * kTileH + r0 + y;
                 if (gy < P.H) {
                     double* dst = P.out + (size_t)(gy + P.g) * P.pitch + P.lead + gx;
-                    *reinterpret_cast<double2*>(dst) = res[y];
+                    if (P.debug & 4) ptx::st_cs_v2f64(dst, res[y].x, res[y].y);   // streaming store
+                    else *reinterpret_cast<double2*>(dst) = res[y];
                 }
             }
         }
