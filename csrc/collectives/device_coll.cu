@@ -1,0 +1,394 @@
+// Collectives on DEVICE tensors over peer-mapped symmetric memory.
+//
+// Reference capability: MPI_Reduce / MPI_Allreduce / MPI_Gather / MPI_Bcast /
+// (MPI_Scatter) / barrier semantics (mpicuda2.cu:154,293, mpi9.cpp:51-54,
+// mpi6.cpp:89-100, mpicuda3.cu:179,316) -- in the reference always on HOST
+// scalars after a D2H copy.  Here the operands stay on the GPUs:
+//   allreduce / reduce   one-shot  (every rank reads all P staged inputs, fixed
+//                                   rank-order sum -> bit-identical everywhere)
+//                        two-shot  (rank r reduces chunk r and stores it into all
+//                                   peers' output staging; large messages)
+//   bcast / gather / allgather / scatter
+//                        push kernel (stores into peers' staging) + epoch flags
+//   barrier              epoch flags only
+// Every kernel signals with st.release.sys / waits with ld.acquire.sys on flags in
+// the peers' workspaces; nothing goes through the host.  `phases` splits
+// signal and wait for single-GPU emulation of several ranks.
+//
+// Workspace (symmetric, one per rank):
+//   [0,512)      ready[P]     epoch of the staged input of rank p   (written by p)
+//   [512,1024)   done[P]      epoch of rank p's reduced chunk       (written by p)
+//   [1024,1536)  bar[P]       barrier epochs
+//   [1536,2048)  data[P]      epoch of pushed data (bcast/gather/scatter)
+//   [2048,2052)  CTA arrival counter (local use)    [2112,2116) status
+//   [4096, ...)  IN[2][cap]  then OUT[2][cap]   (parity = epoch & 1)
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <algorithm>
+#include <new>
+#include <string>
+
+#include "b200comm.h"
+#include "b200comm/error.hpp"
+#include "core/capi_util.hpp"
+#include "kernels/ptx.cuh"
+
+namespace b200 {
+namespace coll {
+
+constexpr int kMaxRanks = 64;
+constexpr size_t kOffReady = 0, kOffDone = 512, kOffBar = 1024, kOffData = 1536, kOffCounter = 2048,
+                 kOffStatus = 2112, kOffStaging = 4096;
+constexpr int kThreads = 256;
+
+struct Ws {
+    unsigned char* peer[kMaxRanks];   // every rank's workspace as mapped here
+    int rank, nranks;
+    size_t cap;                       // bytes of one staging half
+    uint64_t timeout_ns;
+};
+
+__device__ __forceinline__ uint64_t* flag_at(const Ws& w, int owner, size_t region, int idx) {
+    return reinterpret_cast<uint64_t*>(w.peer[owner] + region) + idx;
+}
+__device__ __forceinline__ unsigned char* in_half(const Ws& w, int owner, uint64_t epoch) {
+    return w.peer[owner] + kOffStaging + (epoch & 1) * w.cap;
+}
+__device__ __forceinline__ unsigned char* out_half(const Ws& w, int owner, uint64_t epoch) {
+    return w.peer[owner] + kOffStaging + 2 * w.cap + (epoch & 1) * w.cap;
+}
+
+__device__ __forceinline__ void wait_flag(const Ws& w, const uint64_t* f, uint64_t epoch) {
+    const uint64_t t0 = ptx::globaltimer_ns();
+    uint32_t spins = 0;
+    while (ptx::ld_acquire_sys(f) < epoch) {
+        if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > w.timeout_ns) {
+            atomicOr(reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffStatus), 8u);
+            break;
+        }
+    }
+}
+
+// Tell every rank (incl. myself) that my slot of `region` reached `epoch`.
+__device__ __forceinline__ void signal_all(const Ws& w, size_t region, uint64_t epoch) {
+    for (int r = threadIdx.x; r < w.nranks; r += blockDim.x)
+        ptx::st_release_sys(flag_at(w, r, region, w.rank), epoch);
+}
+// Wait until every rank's slot of `region` in MY workspace reached `epoch`.
+__device__ __forceinline__ void wait_all(const Ws& w, size_t region, uint64_t epoch) {
+    if ((int)threadIdx.x < w.nranks) wait_flag(w, flag_at(w, w.rank, region, threadIdx.x), epoch);
+    __syncthreads();
+}
+
+template <typename T> __device__ __forceinline__ T apply(T a, T b, int op) {
+    switch (op) {
+        case 0: return a + b;
+        case 1: return a * b;
+        case 2: return a > b ? a : b;
+        default: return a < b ? a : b;
+    }
+}
+
+// ---- one-shot allreduce / reduce ------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __grid_constant__ Ws w, T* out,
+                                                                     int64_t n, int op, int root,
+                                                                     uint64_t epoch, int phases) {
+    if (phases & 1) {
+        // the input was staged by an earlier operation in this stream: publish it
+        if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
+    }
+    if (!(phases & 2)) return;
+    if (root >= 0 && w.rank != root) return;
+    wait_all(w, kOffReady, epoch);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        T acc = *reinterpret_cast<const volatile T*>(reinterpret_cast<const T*>(in_half(w, 0, epoch)) + i);
+        for (int r = 1; r < w.nranks; ++r)   // fixed rank order: same bits on every rank
+            acc = apply(acc, *reinterpret_cast<const volatile T*>(
+                                 reinterpret_cast<const T*>(in_half(w, r, epoch)) + i), op);
+        out[i] = acc;
+    }
+}
+
+// ---- two-shot allreduce: reduce-scatter into everybody's OUT, then copy out -----
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(const __grid_constant__ Ws w, T* out,
+                                                                     int64_t n, int op, uint64_t epoch,
+                                                                     int phases) {
+    const int P = w.nranks;
+    const int64_t chunk = (n + P - 1) / P;
+    const int64_t lo = (int64_t)w.rank * chunk, hi = min(n, lo + chunk);
+    __shared__ bool last;
+    if (phases & 1) {
+        if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
+    }
+    if (phases & 2) {
+        wait_all(w, kOffReady, epoch);
+        for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
+             i += (int64_t)gridDim.x * blockDim.x) {
+            T acc = *reinterpret_cast<const volatile T*>(reinterpret_cast<const T*>(in_half(w, 0, epoch)) + i);
+            for (int r = 1; r < P; ++r)
+                acc = apply(acc, *reinterpret_cast<const volatile T*>(
+                                     reinterpret_cast<const T*>(in_half(w, r, epoch)) + i), op);
+            for (int r = 0; r < P; ++r) reinterpret_cast<T*>(out_half(w, r, epoch))[i] = acc;
+        }
+        // my chunk is complete when the LAST CTA has stored it
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            ptx::fence_acq_rel_sys();
+            unsigned int* cnt = reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffCounter);
+            last = atomicInc(cnt, gridDim.x - 1) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (last) signal_all(w, kOffDone, epoch);
+    }
+    if (phases & 4) {
+        wait_all(w, kOffDone, epoch);
+        const T* src = reinterpret_cast<const T*>(out_half(w, w.rank, epoch));
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+             i += (int64_t)gridDim.x * blockDim.x)
+            out[i] = *reinterpret_cast<const volatile T*>(src + i);
+    }
+}
+
+// ---- push: copy `bytes` of local `src` into OUT[parity] + dst_off of the ranks in
+// `targets` (bit mask over ranks, up to 64), then publish data[my rank] there ------
+struct PushArgs {
+    const unsigned char* src;
+    size_t bytes;
+    size_t dst_off[kMaxRanks];   // per target: offset inside its OUT half
+    size_t src_off[kMaxRanks];   // per target: offset inside src (scatter)
+    unsigned long long targets;
+};
+
+__global__ void __launch_bounds__(kThreads) push_kernel(const __grid_constant__ Ws w,
+                                                        const __grid_constant__ PushArgs a,
+                                                        uint64_t epoch) {
+    __shared__ bool last;
+    for (int r = 0; r < w.nranks; ++r) {
+        if (!(a.targets >> r & 1ull)) continue;
+        unsigned char* dst = out_half(w, r, epoch) + a.dst_off[r];
+        const unsigned char* src = a.src + a.src_off[r];
+        const bool al = ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0);
+        const size_t nv = al ? a.bytes / 16 : 0;
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+             i += (size_t)gridDim.x * blockDim.x)
+            ptx::st_v4(reinterpret_cast<int4*>(dst) + i, ptx::ld_nc_v4(reinterpret_cast<const int4*>(src) + i));
+        for (size_t b = nv * 16 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < a.bytes;
+             b += (size_t)gridDim.x * blockDim.x)
+            dst[b] = src[b];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::fence_acq_rel_sys();
+        unsigned int* cnt = reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffCounter);
+        last = atomicInc(cnt, gridDim.x - 1) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last)
+        for (int r = threadIdx.x; r < w.nranks; r += blockDim.x)
+            if (a.targets >> r & 1ull) ptx::st_release_sys(flag_at(w, r, kOffData, w.rank), epoch);
+}
+
+// Wait for data[source] >= epoch for the ranks in `sources`, then copy `bytes` from
+// my OUT half (+ src_off) to `dst`.
+__global__ void __launch_bounds__(kThreads) pull_local_kernel(const __grid_constant__ Ws w,
+                                                              unsigned char* dst, size_t src_off,
+                                                              size_t bytes, unsigned long long sources,
+                                                              uint64_t epoch) {
+    if ((int)threadIdx.x < w.nranks && (sources >> threadIdx.x & 1ull))
+        wait_flag(w, flag_at(w, w.rank, kOffData, threadIdx.x), epoch);
+    __syncthreads();
+    const unsigned char* src = out_half(w, w.rank, epoch) + src_off;
+    const bool al = ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0);
+    const size_t nv = al ? bytes / 16 : 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+         i += (size_t)gridDim.x * blockDim.x)
+        reinterpret_cast<int4*>(dst)[i] = __ldcv(reinterpret_cast<const int4*>(src) + i);
+    for (size_t b = nv * 16 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < bytes;
+         b += (size_t)gridDim.x * blockDim.x)
+        dst[b] = *reinterpret_cast<const volatile unsigned char*>(src + b);
+}
+
+__global__ void barrier_kernel(const __grid_constant__ Ws w, uint64_t epoch, int phases) {
+    if (phases & 1) signal_all(w, kOffBar, epoch);
+    if (phases & 2) wait_all(w, kOffBar, epoch);
+}
+
+struct Plan {
+    Ws ws;
+    int device, sms;
+    uint64_t epoch;        // reductions
+    uint64_t data_epoch;   // push-type collectives
+    uint64_t bar_epoch;
+};
+
+static size_t elem_size(int dtype) { return dtype == 8 || dtype == 5 ? 4 : 8; }
+
+template <typename T>
+static void launch_allreduce(Plan& p, void* out, int64_t n, int op, int root, int algo, int phases,
+                             cudaStream_t st) {
+    // two-shot CTAs wait (phase 4) for a flag that needs EVERY CTA of this grid to have
+    // finished phase 2: the grid must be co-resident, so stay well below capacity
+    const int per_sm = (algo == 1 && root < 0) ? 2 : 4;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + kThreads - 1) / kThreads, p.sms * per_sm));
+    if (algo == 1 && root < 0)
+        allreduce_twoshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, p.epoch, phases);
+    else
+        allreduce_oneshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, root,
+                                                               p.epoch, phases);
+    B200_CHECK_LAUNCH();
+}
+
+}  // namespace coll
+}  // namespace b200
+
+using namespace b200;
+using namespace b200::coll;
+
+struct b2c_coll { Plan p; };
+
+extern "C" {
+
+B2C_EXPORT int b2c_coll_workspace_bytes(size_t max_bytes, size_t* bytes) {
+    B2C_TRY
+    B200_REQUIRE(bytes, ERR_ARG, "null output");
+    const size_t cap = (max_bytes + 255) & ~(size_t)255;
+    *bytes = kOffStaging + 4 * cap;
+    B2C_CATCH
+}
+
+// `workspaces[r]` = rank r's workspace as mapped in this process; all zero-initialised.
+B2C_EXPORT int b2c_coll_create(b2c_coll** out, int rank, int nranks, void* const* workspaces,
+                               size_t max_bytes) {
+    B2C_TRY
+    B200_REQUIRE(out && workspaces, ERR_ARG, "null argument");
+    B200_REQUIRE(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks, ERR_RANK, "bad rank");
+    auto* h = new (std::nothrow) b2c_coll();
+    B200_REQUIRE(h, ERR_NOMEM, "allocation failed");
+    Plan& p = h->p;
+    p = Plan{};
+    for (int r = 0; r < nranks; ++r) p.ws.peer[r] = static_cast<unsigned char*>(workspaces[r]);
+    p.ws.rank = rank; p.ws.nranks = nranks;
+    p.ws.cap = (max_bytes + 255) & ~(size_t)255;
+    p.ws.timeout_ns = 20ull * 1000 * 1000 * 1000;
+    B200_CHECK_CUDA(cudaGetDevice(&p.device));
+    B200_CHECK_CUDA(cudaDeviceGetAttribute(&p.sms, cudaDevAttrMultiProcessorCount, p.device));
+    *out = h;
+    B2C_CATCH
+}
+B2C_EXPORT int b2c_coll_destroy(b2c_coll* h) { B2C_TRY delete h; B2C_CATCH }
+
+// dtype: 5 int32, 6 int64, 8 float32, 9 float64.  op: 0 SUM 1 PROD 2 MAX 3 MIN.
+// algo: 0 one-shot, 1 two-shot.  root < 0: allreduce.  `in` and `out` are LOCAL
+// device pointers (they may alias).  phases: 7 = all in one call; for several
+// emulated ranks on one GPU call with 1 (stage+publish) on every rank, then 2,
+// then 4 (one-shot ignores 4).
+B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_t count, int dtype,
+                                  int op, int root, int algo, int phases, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h && in && out && count >= 0, ERR_ARG, "bad argument");
+    B200_REQUIRE(dtype == 5 || dtype == 6 || dtype == 8 || dtype == 9, ERR_TYPE,
+                 "device reductions support int32, int64, float32, float64");
+    B200_REQUIRE(op >= 0 && op <= 3, ERR_ARG, "device reductions support SUM, PROD, MAX, MIN");
+    Plan& p = h->p;
+    const size_t bytes = (size_t)count * elem_size(dtype);
+    B200_REQUIRE(bytes <= p.ws.cap, ERR_COUNT,
+                 "message of " + std::to_string(bytes) + " B exceeds the collective workspace (" +
+                     std::to_string(p.ws.cap) + " B)");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (phases & 1) {
+        p.epoch += 1;
+        unsigned char* stage = p.ws.peer[p.ws.rank] + kOffStaging + (p.epoch & 1) * p.ws.cap;
+        B200_CHECK_CUDA(cudaMemcpyAsync(stage, in, bytes, cudaMemcpyDeviceToDevice, st));
+    }
+    switch (dtype) {
+        case 9: launch_allreduce<double>(p, out, count, op, root, algo, phases, st); break;
+        case 8: launch_allreduce<float>(p, out, count, op, root, algo, phases, st); break;
+        case 6: launch_allreduce<long long>(p, out, count, op, root, algo, phases, st); break;
+        default: launch_allreduce<int>(p, out, count, op, root, algo, phases, st); break;
+    }
+    B2C_CATCH
+}
+
+// kind: 0 bcast (root pushes `bytes` to everybody), 1 gather (everybody pushes its block to
+// root's slot `rank`), 2 allgather, 3 scatter (root pushes block r to rank r).
+// phases: 1 = push, 2 = wait + copy out.  `buf` is the send buffer for pushers and the
+// receive buffer for receivers (bcast: same buffer; gather: sendbuf/recvbuf given separately).
+B2C_EXPORT int b2c_coll_move(b2c_coll* h, int kind, const void* sendbuf, void* recvbuf,
+                             size_t block_bytes, int root, int phases, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null handle");
+    B200_REQUIRE(kind >= 0 && kind <= 3, ERR_ARG, "unknown collective kind");
+    Plan& p = h->p;
+    const int P = p.ws.nranks, me = p.ws.rank;
+    B200_REQUIRE(kind == 2 || (root >= 0 && root < P), ERR_RANK, "invalid root");
+    const size_t total = (kind == 0) ? block_bytes : block_bytes * (size_t)P;
+    B200_REQUIRE(total <= p.ws.cap, ERR_COUNT, "message exceeds the collective workspace");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (phases & 1) p.data_epoch += 1;
+    const uint64_t epoch = p.data_epoch;
+    const unsigned long long all = P == 64 ? ~0ull : ((1ull << P) - 1);
+    if (phases & 1) {
+        PushArgs a{};
+        a.src = static_cast<const unsigned char*>(sendbuf);
+        a.bytes = block_bytes;
+        bool pusher = false;
+        if (kind == 0 && me == root) { a.targets = all; pusher = true; }
+        if (kind == 1) { a.targets = 1ull << root; a.dst_off[root] = (size_t)me * block_bytes; pusher = true; }
+        if (kind == 2) { a.targets = all; for (int r = 0; r < P; ++r) a.dst_off[r] = (size_t)me * block_bytes; pusher = true; }
+        if (kind == 3 && me == root) {
+            a.targets = all;
+            for (int r = 0; r < P; ++r) a.src_off[r] = (size_t)r * block_bytes;
+            pusher = true;
+        }
+        if (pusher) {
+            B200_REQUIRE(sendbuf != nullptr || block_bytes == 0, ERR_BUFFER, "null send buffer");
+            const int grid = (int)std::max<size_t>(1, std::min<size_t>((block_bytes / 16 + kThreads - 1) / kThreads, (size_t)p.sms * 2));
+            push_kernel<<<grid, kThreads, 0, st>>>(p.ws, a, epoch);
+            B200_CHECK_LAUNCH();
+        }
+    }
+    if (phases & 2) {
+        unsigned long long sources = 0;
+        size_t bytes = 0;
+        if (kind == 0) { sources = 1ull << root; bytes = block_bytes; }
+        if (kind == 1 && me == root) { sources = all; bytes = total; }
+        if (kind == 2) { sources = all; bytes = total; }
+        if (kind == 3) { sources = 1ull << root; bytes = block_bytes; }
+        if (sources) {
+            B200_REQUIRE(recvbuf != nullptr || bytes == 0, ERR_BUFFER, "null receive buffer");
+            const int grid = (int)std::max<size_t>(1, std::min<size_t>((bytes / 16 + kThreads - 1) / kThreads, (size_t)p.sms * 2));
+            pull_local_kernel<<<grid, kThreads, 0, st>>>(p.ws, static_cast<unsigned char*>(recvbuf), 0,
+                                                         bytes, sources, epoch);
+            B200_CHECK_LAUNCH();
+        }
+    }
+    B2C_CATCH
+}
+
+B2C_EXPORT int b2c_coll_barrier(b2c_coll* h, int phases, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null handle");
+    Plan& p = h->p;
+    if (phases & 1) p.bar_epoch += 1;
+    barrier_kernel<<<1, 64, 0, (cudaStream_t)stream>>>(p.ws, p.bar_epoch, phases);
+    B200_CHECK_LAUNCH();
+    B2C_CATCH
+}
+
+// Synchronises the stream and reports device-side time-outs.
+B2C_EXPORT int b2c_coll_check(b2c_coll* h, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null handle");
+    unsigned int st = 0;
+    B200_CHECK_CUDA(cudaMemcpyAsync(&st, h->p.ws.peer[h->p.ws.rank] + kOffStatus, 4,
+                                    cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    B200_REQUIRE((st & 8u) == 0, ERR_TIMEOUT, "device collective: a peer never arrived");
+    B2C_CATCH
+}
+
+}  // extern "C"

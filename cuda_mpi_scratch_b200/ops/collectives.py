@@ -1,0 +1,195 @@
+"""Collectives on CUDA tensors over peer-mapped symmetric memory (no host, no NCCL).
+
+Capability parity with ``MPI_Reduce`` / ``MPI_Allreduce`` / ``MPI_Gather`` /
+``MPI_Bcast`` / ``MPI_Scatter`` as used by the reference (``mpicuda2.cu:154,293``,
+``mpi9.cpp:51-54``, ``mpi6.cpp:89-100``) -- there always on host scalars after a
+device-to-host copy.  Here the operands stay on the GPUs: inputs are staged in a
+symmetric workspace, kernels read/write the peers' staging directly and
+synchronise with epoch flags.  Reductions add in rank order, so every rank gets
+bit-identical results.
+
+``allreduce`` picks one-shot (every rank reads all inputs) below
+``twoshot_min_bytes`` and two-shot (reduce-scatter + broadcast of the reduced
+chunks) above it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _lib
+from ..parallel.symmetric import SymmetricBuffer
+from ..parallel.world import LocalGroup, World
+
+_L = _lib.lib
+_vp, _i32, _i64 = C.c_void_p, C.c_int, C.c_int64
+_lib._proto("b2c_coll_workspace_bytes", [C.c_size_t, C.POINTER(C.c_size_t)])
+_lib._proto("b2c_coll_create", [C.POINTER(_vp), _i32, _i32, C.POINTER(_vp), C.c_size_t])
+_lib._proto("b2c_coll_destroy", [_vp])
+_lib._proto("b2c_coll_allreduce", [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp])
+_lib._proto("b2c_coll_move", [_vp, _i32, _vp, _vp, C.c_size_t, _i32, _i32, _vp])
+_lib._proto("b2c_coll_barrier", [_vp, _i32, _vp])
+_lib._proto("b2c_coll_check", [_vp, _vp])
+
+_DT = {torch.int32: 5, torch.int64: 6, torch.float32: 8, torch.float64: 9}
+OPS = {"sum": 0, "prod": 1, "max": 2, "min": 3}
+BCAST, GATHER, ALLGATHER, SCATTER = range(4)
+
+
+def workspace_bytes(max_bytes: int) -> int:
+    n = C.c_size_t()
+    _lib.check(_L.b2c_coll_workspace_bytes(max_bytes, C.byref(n)))
+    return n.value
+
+
+def _stream(device: int) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+class DeviceCollectives:
+    """One rank's handle.  All calls are stream-ordered on the current torch stream."""
+
+    def __init__(self, rank: int, nranks: int, symbuf: SymmetricBuffer, max_bytes: int,
+                 world: World | None, twoshot_min_bytes: int = 512 << 10):
+        self.rank, self.nranks, self.symbuf, self.max_bytes = rank, nranks, symbuf, max_bytes
+        self.world, self.device = world, symbuf.device
+        self.twoshot_min_bytes = twoshot_min_bytes
+        ws = (C.c_void_p * nranks)(*[symbuf.peer_ptr(r) for r in range(nranks)])
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_create(C.byref(h), rank, nranks, ws, max_bytes))
+        self._h = h
+        self.kernel_launches = 0
+
+    @classmethod
+    def create(cls, world: World, max_bytes: int = 64 << 20, **kw) -> "DeviceCollectives":
+        sym = SymmetricBuffer.allocate(world, workspace_bytes(max_bytes))
+        return cls(world.rank, world.size, sym, max_bytes, world, **kw)
+
+    @classmethod
+    def create_group(cls, group: LocalGroup, max_bytes: int = 16 << 20, **kw) -> "CollectiveGroup":
+        syms = SymmetricBuffer.allocate_local(group, workspace_bytes(max_bytes))
+        return CollectiveGroup([cls(r, group.size, syms[r], max_bytes, None, **kw)
+                                for r in range(group.size)])
+
+    # ---- reductions ----------------------------------------------------------
+    def _algo(self, t: torch.Tensor, algo: str) -> int:
+        if algo == "auto":
+            return 1 if t.numel() * t.element_size() >= self.twoshot_min_bytes and self.nranks > 1 else 0
+        return {"oneshot": 0, "twoshot": 1}[algo]
+
+    def allreduce(self, t: torch.Tensor, op: str = "sum", algo: str = "auto", out: torch.Tensor | None = None,
+                  phases: int = 7, root: int = -1) -> torch.Tensor:
+        """In-place (or into ``out``) all-reduce of a contiguous CUDA tensor."""
+        if t.dtype not in _DT or not t.is_contiguous():
+            raise TypeError("need a contiguous int32/int64/float32/float64 CUDA tensor")
+        out = t if out is None else out
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_allreduce(self._h, t.data_ptr(), out.data_ptr(), t.numel(), _DT[t.dtype],
+                                             OPS[op], root, self._algo(t, algo) if root < 0 else 0,
+                                             phases, _stream(self.device)))
+        self.kernel_launches += 1
+        return out
+
+    def reduce(self, t: torch.Tensor, root: int, op: str = "sum", out: torch.Tensor | None = None,
+               phases: int = 7) -> torch.Tensor | None:
+        """``MPI_Reduce``: the result is written on ``root`` only."""
+        res = self.allreduce(t, op, "oneshot", out if out is not None else t, phases, root)
+        return res if self.rank == root else None
+
+    # ---- data movement ---------------------------------------------------------
+    def _move(self, kind, send, recv, block_bytes, root, phases):
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_move(self._h, kind, None if send is None else send.data_ptr(),
+                                        None if recv is None else recv.data_ptr(), block_bytes, root,
+                                        phases, _stream(self.device)))
+        self.kernel_launches += 2
+
+    def bcast(self, t: torch.Tensor, root: int = 0, phases: int = 3) -> torch.Tensor:
+        self._move(BCAST, t, t, t.numel() * t.element_size(), root, phases)
+        return t
+
+    def gather(self, send: torch.Tensor, recv: torch.Tensor | None, root: int = 0, phases: int = 3):
+        """Non-root ranks may pass ``recv=None`` (``mpi6.cpp:96-100``)."""
+        self._move(GATHER, send, recv, send.numel() * send.element_size(), root, phases)
+        return recv
+
+    def allgather(self, send: torch.Tensor, recv: torch.Tensor, phases: int = 3) -> torch.Tensor:
+        self._move(ALLGATHER, send, recv, send.numel() * send.element_size(), 0, phases)
+        return recv
+
+    def scatter(self, send: torch.Tensor | None, recv: torch.Tensor, root: int = 0, phases: int = 3):
+        self._move(SCATTER, send, recv, recv.numel() * recv.element_size(), root, phases)
+        return recv
+
+    def barrier(self, phases: int = 3) -> None:
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_barrier(self._h, phases, _stream(self.device)))
+        self.kernel_launches += 1
+
+    def check(self) -> None:
+        """Synchronise and raise ``ERR_TIMEOUT`` if a peer never arrived."""
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_check(self._h, _stream(self.device)))
+
+    def close(self) -> None:
+        if self._h:
+            _L.b2c_coll_destroy(self._h)
+            self._h = None
+
+
+class CollectiveGroup:
+    """Virtual ranks in one process: every collective is issued phase by phase over
+    all ranks, so no kernel waits for one that has not been launched."""
+
+    def __init__(self, ranks: list[DeviceCollectives]):
+        self.ranks = ranks
+
+    def _sync(self):
+        for d in {r.device for r in self.ranks}:
+            torch.cuda.synchronize(d)
+
+    def allreduce(self, ts: list[torch.Tensor], op="sum", algo="auto") -> list[torch.Tensor]:
+        for ph in (1, 2, 4):
+            for r, t in zip(self.ranks, ts):
+                r.allreduce(t, op, algo, phases=ph)
+            self._sync()
+        return ts
+
+    def reduce(self, ts, root, op="sum"):
+        for ph in (1, 2):
+            for r, t in zip(self.ranks, ts):
+                r.reduce(t, root, op, phases=ph)
+            self._sync()
+        return ts[root]
+
+    def _two_phase(self, fn):
+        for ph in (1, 2):
+            fn(ph)
+            self._sync()
+
+    def bcast(self, ts, root=0):
+        self._two_phase(lambda ph: [r.bcast(t, root, ph) for r, t in zip(self.ranks, ts)])
+        return ts
+
+    def gather(self, sends, recv, root=0):
+        self._two_phase(lambda ph: [r.gather(s, recv if r.rank == root else None, root, ph)
+                                    for r, s in zip(self.ranks, sends)])
+        return recv
+
+    def allgather(self, sends, recvs):
+        self._two_phase(lambda ph: [r.allgather(s, o, ph) for r, s, o in zip(self.ranks, sends, recvs)])
+        return recvs
+
+    def scatter(self, send, recvs, root=0):
+        self._two_phase(lambda ph: [r.scatter(send if r.rank == root else None, o, root, ph)
+                                    for r, o in zip(self.ranks, recvs)])
+        return recvs
+
+    def barrier(self):
+        self._two_phase(lambda ph: [r.barrier(ph) for r in self.ranks])
+
+    def check(self):
+        for r in self.ranks:
+            r.check()

@@ -251,6 +251,24 @@ int b2c_move_uniform(const void* src, void* dst, int64_t nruns, int64_t len, int
 int b2c_move_segments(const void* src, void* dst, const void* dev_segments, int64_t nseg,
                       int64_t max_len, int64_t items_64k, void* stream);
 
+/* ------------------------------------------------------ device collectives */
+/* Collectives on DEVICE tensors through peer-mapped staging + epoch flags (no host,
+ * no NCCL).  Reference capability: MPI_Reduce / MPI_Allreduce / MPI_Gather /
+ * MPI_Bcast / MPI_Scatter (mpicuda2.cu:154,293, mpi9.cpp:51-54, mpi6.cpp:89-100),
+ * which the reference only ever applies to host scalars after a D2H copy.
+ * dtype 5 int32, 6 int64, 8 float32, 9 float64; op 0 SUM 1 PROD 2 MAX 3 MIN;
+ * algo 0 one-shot, 1 two-shot; kind 0 bcast 1 gather 2 allgather 3 scatter.     */
+typedef struct b2c_coll b2c_coll;
+int b2c_coll_workspace_bytes(size_t max_bytes, size_t* bytes);
+int b2c_coll_create(b2c_coll** out, int rank, int nranks, void* const* workspaces, size_t max_bytes);
+int b2c_coll_destroy(b2c_coll* c);
+int b2c_coll_allreduce(b2c_coll* c, const void* in, void* out, int64_t count, int dtype, int op,
+                       int root /* <0: allreduce */, int algo, int phases, void* stream);
+int b2c_coll_move(b2c_coll* c, int kind, const void* sendbuf, void* recvbuf, size_t block_bytes,
+                  int root, int phases, void* stream);
+int b2c_coll_barrier(b2c_coll* c, int phases, void* stream);
+int b2c_coll_check(b2c_coll* c, void* stream);
+
 /* -------------------------------------------------------- distributed dot */
 /* Dot product whose local reduction is fused with a one-shot P2P allreduce
  * (or reduce-to-root) in ONE kernel per rank.  Reference capability:
