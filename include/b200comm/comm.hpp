@@ -21,6 +21,7 @@
 #include "b200comm/datatype.hpp"
 #include "b200comm/error.hpp"
 
+#pragma GCC visibility push(default)   // public C++ API: exported from the library
 namespace b200 {
 namespace comm {
 
@@ -149,3 +150,4 @@ std::string processor_name();
 
 }  // namespace comm
 }  // namespace b200
+#pragma GCC visibility pop

@@ -16,6 +16,7 @@
 #include <string>
 #include <vector>
 
+#pragma GCC visibility push(default)   // public C++ API: exported from the library
 namespace b200 {
 
 struct Run {
@@ -97,3 +98,4 @@ struct Segment {
 std::vector<Segment> merge_runs(const std::vector<Run>& src, const std::vector<Run>& dst);
 
 }  // namespace b200
+#pragma GCC visibility pop

@@ -12,6 +12,7 @@
 #include <stdexcept>
 #include <string>
 
+#pragma GCC visibility push(default)   // public C++ API: exported from the library
 namespace b200 {
 
 // Error classes (the analogue of MPI error classes, mpierr.h:23-25).
@@ -67,6 +68,7 @@ void set_last_error(const std::string& s) noexcept;
 const char* last_error() noexcept;
 
 }  // namespace b200
+#pragma GCC visibility pop
 
 #define B200_FAIL(code, msg) ::b200::fail_comm((code), (msg), __FILE__, __LINE__)
 #define B200_REQUIRE(cond, code, msg)                                   \

@@ -29,6 +29,7 @@
 #define B200_HD
 #endif
 
+#pragma GCC visibility push(default)   // public C++ API: exported from the library
 namespace b200 {
 namespace stencil2d {
 
@@ -130,3 +131,4 @@ std::string region_report(int w, int h, int stencilWidth, int stencilHeight);
 
 }  // namespace stencil2d
 }  // namespace b200
+#pragma GCC visibility pop
