@@ -19,6 +19,10 @@
 #include "b200comm/error.hpp"
 #include "core/capi_util.hpp"
 #include "stencil/stencil_kernel.cuh"
+#include "stencil/stencil_strip_kernel.cuh"
+
+#include <algorithm>
+#include <vector>
 
 namespace b200 {
 namespace stencil {
@@ -197,7 +201,158 @@ struct Plan {
     size_t smem;
     uint64_t timeout_ns;
     int tilesX, tilesY;
+    uint64_t contrib[8];         // signals per step a neighbour sends me per direction
+    // ---- strip kernel (algo 1) ----
+    int algo;                    // 0 tile kernel, 1 strip kernel
+    CUtensorMap strip_tmap[2];
+    Segment* d_segs;
+    int* d_seg_begin;
+    int strip_grid, strip_slots;
+    int strip_w;                 // cells per strip of this plan (even, <= kStripW)
+    size_t strip_smem;
 };
+
+// Strip width such that (interior strips) x (row bands) uses as many of the G CTAs as
+// possible: every CTA then owns one long segment and all CTAs of a band advance together.
+static int choose_strip_width(int W, int H, int R, int G) {
+    const int wmax = std::min(kStripW, W);
+    int best_w = wmax & ~1, best_busy = -1;
+    const int CY = (H + kChunkH - 1) / kChunkH;
+    for (int NB = 1; NB <= 16; ++NB) {
+        const int NSi = G / NB;
+        if (NSi < 1 || CY - 2 < 8 * NB) continue;
+        int sw = ((W + (NSi + 2) - 1) / (NSi + 2) + 1) & ~1;     // ceil(W / NS), rounded up to even
+        if (sw > wmax || sw < 64) continue;
+        const int NS = (W + sw - 1) / sw;
+        const int last = W - (NS - 1) * sw;
+        if (NS < 3 || (last != sw && last < R)) continue;
+        const int busy = std::min(NS - 2, NSi) * NB;
+        if (busy > best_busy || (busy == best_busy && sw > best_w)) { best_busy = busy; best_w = sw; }
+    }
+    return best_w;
+}
+
+constexpr int kStripSlots = 6;
+
+// Work partition of the strip kernel: every CTA gets its boundary segments first
+// (pieces of the west/east strips, single top/bottom chunks of the interior strips),
+// then one contiguous run of interior chunks.  Also counts, per direction, how many
+// segments signal it -- the neighbour (same geometry) sends me exactly as many.
+static void build_strip_partition(Plan& p, int G, std::vector<Segment>& segs, std::vector<int>& begin) {
+    const int W = p.L.W, H = p.L.H;
+    const int NS = (W + p.strip_w - 1) / p.strip_w, CY = (H + kChunkH - 1) / kChunkH;
+    std::vector<std::vector<Segment>> per((size_t)G);
+    std::vector<long> load((size_t)G, 0);
+    auto act = [&](int d) {
+        const bool corner = dir_dy(d) != 0 && dir_dx(d) != 0;
+        return p.nbr[d] != nullptr && (!corner || p.push_corners);
+    };
+    // Geometric edge mask of a segment; what it actually waits for / pushes to is the
+    // subset with a neighbour.  The per-direction signal COUNT must be geometric: a
+    // neighbour with the same tile geometry sends me that many signals even when my own
+    // opposite side has no neighbour (non-periodic grids).
+    for (int d = 0; d < 8; ++d) p.contrib[d] = 0;
+    unsigned actmask = 0;
+    for (int d = 0; d < 8; ++d) if (act(d)) actmask |= 1u << d;
+    auto dirs_for = [&](int strip, int j0, int j1) {
+        const bool w = strip == 0, e = strip == NS - 1, n = j0 == 0, s = j1 == CY;
+        unsigned m = 0;
+        auto add = [&](bool c, int d) { if (c) m |= 1u << d; };
+        add(n, N); add(s, S); add(w, W_); add(e, E_);
+        add(n && w, NW); add(n && e, NE); add(s && w, SW); add(s && e, SE);
+        for (int d = 0; d < 8; ++d) if (m >> d & 1u) p.contrib[d] += 1;
+        return m & actmask;
+    };
+    int rr = 0;   // round-robin cursor over CTAs
+    auto give = [&](int strip, int j0, int j1) {
+        per[(size_t)rr].push_back(Segment{strip, j0, j1, dirs_for(strip, j0, j1)});
+        load[(size_t)rr] += (j1 - j0) + 2;
+        rr = (rr + 1) % G;
+    };
+    // west / east strips, cut into pieces of >= 4 chunks
+    const int npieces = std::max(1, std::min(G, CY / 4));
+    for (int b = 0; b < (NS > 1 ? 2 : 1); ++b) {
+        const int strip = b == 0 ? 0 : NS - 1;
+        for (int q = 0; q < npieces; ++q) {
+            const int j0 = (int)((long)CY * q / npieces), j1 = (int)((long)CY * (q + 1) / npieces);
+            if (j1 > j0) give(strip, j0, j1);
+        }
+    }
+    // top / bottom chunk of every interior strip
+    for (int strip = 1; strip + 1 < NS; ++strip) {
+        give(strip, 0, 1);
+        if (CY > 1) give(strip, CY - 1, CY);
+    }
+    // interior chunks: strips 1..NS-2, chunks 1..CY-2, strip-major, contiguous per CTA
+    const long ich = (NS > 2 && CY > 2) ? (long)(NS - 2) * (CY - 2) : 0;
+    const char* pe = std::getenv("B2C_STRIP_PART");
+    const int NSi = NS - 2, CYi = CY - 2;
+    const int NB = NSi > 0 ? G / NSi : 0;        // row bands so that bands x strips <= CTAs
+    if (ich > 0 && NB >= 1 && CYi >= 8 * NB && !(pe && std::string(pe) == "run")) {
+        // band-major: CTA (band b, strip s) marches down rows of band b of strip s.  CTAs of
+        // one band sit on ADJACENT strips and advance in lock-step, so at any instant DRAM
+        // sees whole contiguous rows (like the x-fastest tile order), not scattered pieces.
+        for (int b = 0; b < NB; ++b)
+            for (int si = 0; si < NSi; ++si) {
+                const int cta = b * NSi + si;
+                const int j0 = 1 + (int)((long)CYi * b / NB), j1 = 1 + (int)((long)CYi * (b + 1) / NB);
+                per[(size_t)cta].push_back(Segment{1 + si, j0, j1, 0u});
+            }
+    } else if (ich > 0) {
+        long total = ich;
+        for (long l : load) total += l;
+        const long target = (total + G - 1) / G;
+        long next = 0;
+        for (int cta = 0; cta < G && next < ich; ++cta) {
+            long want = target - load[(size_t)cta];
+            if (cta == G - 1) want = ich - next;
+            if (want <= 0) continue;
+            long endi = std::min(ich, next + want);
+            while (next < endi) {   // split at strip boundaries
+                const int strip = 1 + (int)(next / (CY - 2));
+                const int j0 = 1 + (int)(next % (CY - 2));
+                const long room = (CY - 2) - (next % (CY - 2));
+                const long n = std::min(room, endi - next);
+                per[(size_t)cta].push_back(Segment{strip, j0, j0 + (int)n, 0u});
+                next += n;
+            }
+        }
+        // anything left (rounding) goes to the last CTA
+        while (next < ich) {
+            const int strip = 1 + (int)(next / (CY - 2));
+            const int j0 = 1 + (int)(next % (CY - 2));
+            const long n = std::min<long>((CY - 2) - (next % (CY - 2)), ich - next);
+            per[(size_t)G - 1].push_back(Segment{strip, j0, j0 + (int)n, 0u});
+            next += n;
+        }
+    }
+    begin.assign(1, 0);
+    for (int cta = 0; cta < G; ++cta) {
+        for (const Segment& s : per[(size_t)cta]) segs.push_back(s);
+        begin.push_back((int)segs.size());
+    }
+}
+
+template <int R>
+static void launch_strip(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    StripParams sp{};
+    sp.lp = lp;
+    sp.segs = pl.d_segs;
+    sp.seg_begin = pl.d_seg_begin;
+    sp.strip_w = pl.strip_w;
+    sp.box_w = pl.strip_w + 4;
+    auto k0 = stencil_strip_kernel<R, false, kStripSlots>;
+    auto k1 = stencil_strip_kernel<R, true, kStripSlots>;
+    static bool attr_done[64] = {};
+    if (!attr_done[pl.device & 63]) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.strip_smem));
+        B200_CHECK_CUDA(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.strip_smem));
+        attr_done[pl.device & 63] = true;
+    }
+    if (resid) k1<<<pl.strip_grid, kStripThreads, pl.strip_smem, st>>>(pl.strip_tmap[pl.cur], sp);
+    else k0<<<pl.strip_grid, kStripThreads, pl.strip_smem, st>>>(pl.strip_tmap[pl.cur], sp);
+    B200_CHECK_LAUNCH();
+}
 
 template <int R, bool BOX, bool RESID, int NST>
 static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) {
@@ -220,6 +375,11 @@ static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStr
 }
 
 static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.algo == 1) {
+        if (pl.L.R == 1) launch_strip<1>(pl, lp, resid, st);
+        else launch_strip<2>(pl, lp, resid, st);
+        return;
+    }
     if (pl.kind == 0) {
         switch (pl.L.R) {
             case 1: launch_r<1, false>(pl, lp, resid, st); return;
@@ -236,10 +396,15 @@ static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cuda
     B200_FAIL(ERR_ARG, "unsupported stencil kind/radius");
 }
 
-static uint64_t contributions(const Plan& pl, int d) {
-    const int dy = dir_dy(d), dx = dir_dx(d);
-    if (dy != 0 && dx != 0) return 1;
-    return dy != 0 ? (uint64_t)pl.tilesX : (uint64_t)pl.tilesY;
+// Signals per step that arrive on my counter `d` (= what the neighbour in direction d,
+// which has the same tile geometry, sends towards me).
+static uint64_t contributions(const Plan& pl, int d) { return pl.contrib[dir_opposite(d)]; }
+
+static void tile_contributions(Plan& pl) {
+    for (int d = 0; d < 8; ++d) {
+        const int dy = dir_dy(d), dx = dir_dx(d);
+        pl.contrib[d] = (dy != 0 && dx != 0) ? 1 : (dy != 0 ? (uint64_t)pl.tilesX : (uint64_t)pl.tilesY);
+    }
 }
 
 static bool dir_active(const Plan& pl, int d) {
@@ -328,9 +493,54 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         B200_REQUIRE(r == CUDA_SUCCESS, ERR_CUDA,
                      "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
     }
+    tile_contributions(p);
+    // ---- strip kernel: star stencils of radius <= 2 whose edge strips do not straddle
+    // a strip / chunk boundary.  B2C_STENCIL_ALGO=tile|strip overrides the choice.
+    {
+        const char* ae = std::getenv("B2C_STENCIL_ALGO");
+        const char* ge = std::getenv("B2C_STRIP_CTAS_PER_SM");
+        const int per_sm = ge ? std::max(1, std::min(kStripCtasPerSm, std::atoi(ge))) : 2;
+        const long chunks_all = (long)((W + kStripW - 1) / kStripW) * ((H + kChunkH - 1) / kChunkH);
+        p.strip_grid = (int)std::max<long>(1, std::min<long>(prop.multiProcessorCount * per_sm, (chunks_all + 7) / 8));
+        const char* we = std::getenv("B2C_STRIP_WIDTH");
+        p.strip_w = we ? (std::max(2, std::min(kStripW, std::atoi(we))) & ~1)
+                       : choose_strip_width(W, H, R, p.strip_grid);
+        const bool eligible = kind == 0 && R <= 2 &&
+                              (W % p.strip_w == 0 || W % p.strip_w >= R) &&
+                              (H % kChunkH == 0 || H % kChunkH >= R);
+        bool use = eligible;
+        if (ae && std::string(ae) == "tile") use = false;
+        if (ae && std::string(ae) == "strip")
+            B200_REQUIRE(eligible, ERR_ARG, "strip kernel not applicable to this stencil/tile");
+        p.algo = use ? 1 : 0;
+    }
+    if (p.algo == 1) {
+        p.strip_slots = kStripSlots;
+        p.strip_smem = (size_t)kStripSlots * kChunkBytes + 128 + 2 * kStripSlots * sizeof(uint64_t);
+        std::vector<Segment> segs;
+        std::vector<int> begin;
+        build_strip_partition(p, p.strip_grid, segs, begin);
+        B200_CHECK_CUDA(cudaMalloc(&p.d_segs, std::max<size_t>(1, segs.size()) * sizeof(Segment)));
+        B200_CHECK_CUDA(cudaMalloc(&p.d_seg_begin, begin.size() * sizeof(int)));
+        B200_CHECK_CUDA(cudaMemcpy(p.d_segs, segs.data(), segs.size() * sizeof(Segment), cudaMemcpyHostToDevice));
+        B200_CHECK_CUDA(cudaMemcpy(p.d_seg_begin, begin.data(), begin.size() * sizeof(int), cudaMemcpyHostToDevice));
+        for (int b = 0; b < 2; ++b) {
+            cuuint64_t gdim[2] = {(cuuint64_t)p.L.pitch, (cuuint64_t)p.L.rows};
+            cuuint64_t gstr[1] = {(cuuint64_t)p.L.pitch * sizeof(double)};
+            cuuint32_t box[2] = {(cuuint32_t)(p.strip_w + 4), (cuuint32_t)kChunkH};
+            cuuint32_t estr[2] = {1, 1};
+            CUresult r = enc(&p.strip_tmap[b], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, p.base + p.L.off_x[b],
+                             gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            B200_REQUIRE(r == CUDA_SUCCESS, ERR_CUDA,
+                         "cuTensorMapEncodeTiled (strip) failed with CUresult " + std::to_string((int)r));
+        }
+    }
     p.ncoef = kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1);
     B200_CHECK_CUDA(cudaMalloc(&p.coef_dev, 128 * sizeof(double)));
-    B200_CHECK_CUDA(cudaMalloc(&p.resid_partials, (size_t)p.grid * sizeof(double)));
+    B200_CHECK_CUDA(cudaMalloc(&p.resid_partials,
+                               (size_t)std::max(p.grid, p.strip_grid) * sizeof(double)));
     // default: Jacobi average of the 4R (or (2R+1)^2-1) neighbours
     double hc[128] = {0};
     const int nn = p.ncoef - 1;
@@ -346,6 +556,8 @@ B2C_EXPORT int b2c_stencil_destroy(b2c_stencil* h) {
     if (!h) return 0;
     cudaFree(h->p.coef_dev);
     cudaFree(h->p.resid_partials);
+    if (h->p.d_segs) cudaFree(h->p.d_segs);
+    if (h->p.d_seg_begin) cudaFree(h->p.d_seg_begin);
     delete h;
     B2C_CATCH
 }
@@ -371,8 +583,11 @@ B2C_EXPORT int b2c_stencil_info(b2c_stencil* h, b2c_stencil_info_t* o) {
     B2C_TRY
     B200_REQUIRE(h && o, ERR_ARG, "null argument");
     const Plan& p = h->p;
-    o->cur = p.cur; o->steps_done = p.steps_done; o->grid = p.grid; o->threads = kThreads;
-    o->smem_bytes = p.smem; o->nstages = p.nstages; o->tiles_x = p.tilesX; o->tiles_y = p.tilesY;
+    o->cur = p.cur; o->steps_done = p.steps_done;
+    o->grid = p.algo == 1 ? p.strip_grid : p.grid;
+    o->threads = p.algo == 1 ? kStripThreads : kThreads;
+    o->smem_bytes = p.algo == 1 ? p.strip_smem : p.smem;
+    o->nstages = p.algo == 1 ? p.strip_slots : p.nstages; o->tiles_x = p.tilesX; o->tiles_y = p.tilesY;
     o->ncoef = p.ncoef; o->launches_per_step = 1;
     o->buf[0] = p.base + p.L.off_x[0]; o->buf[1] = p.base + p.L.off_x[1];
     o->resid = reinterpret_cast<double*>(p.base + kOffResid);
@@ -452,7 +667,7 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         const bool resid = (flags & 1) && s == nsteps - 1;
         launch_step(p, lp, resid, st);
         if (resid) {
-            sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials, p.grid,
+            sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials, p.algo == 1 ? p.strip_grid : p.grid,
                                                    reinterpret_cast<double*>(p.base + kOffResid));
             B200_CHECK_LAUNCH();
         }
