@@ -232,7 +232,7 @@ static int choose_strip_width(int W, int H, int R, int G) {
     return best_w;
 }
 
-constexpr int kStripSlots = 6;
+constexpr int kStripSlots = 5;   // default ring depth (B2C_STRIP_SLOTS = 3..6 | 8 | 10 | 12); deeper is SLOWER, see profiles/
 
 // Work partition of the strip kernel: every CTA gets its boundary segments first
 // (pieces of the west/east strips, single top/bottom chunks of the interior strips),
@@ -333,16 +333,32 @@ static void build_strip_partition(Plan& p, int G, std::vector<Segment>& segs, st
     }
 }
 
+template <int R, int SLOTS>
+static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st);
+
 template <int R>
 static void launch_strip(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    switch (pl.strip_slots) {
+        case 3: launch_strip_s<R, 3>(pl, lp, resid, st); return;
+        case 4: launch_strip_s<R, 4>(pl, lp, resid, st); return;
+        case 5: launch_strip_s<R, 5>(pl, lp, resid, st); return;
+        case 6: launch_strip_s<R, 6>(pl, lp, resid, st); return;
+        case 8: launch_strip_s<R, 8>(pl, lp, resid, st); return;
+        case 10: launch_strip_s<R, 10>(pl, lp, resid, st); return;
+        default: launch_strip_s<R, 12>(pl, lp, resid, st); return;
+    }
+}
+
+template <int R, int SLOTS>
+static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
     StripParams sp{};
     sp.lp = lp;
     sp.segs = pl.d_segs;
     sp.seg_begin = pl.d_seg_begin;
     sp.strip_w = pl.strip_w;
     sp.box_w = pl.strip_w + 4;
-    auto k0 = stencil_strip_kernel<R, false, kStripSlots>;
-    auto k1 = stencil_strip_kernel<R, true, kStripSlots>;
+    auto k0 = stencil_strip_kernel<R, false, SLOTS>;
+    auto k1 = stencil_strip_kernel<R, true, SLOTS>;
     static bool attr_done[64] = {};
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.strip_smem));
@@ -515,8 +531,12 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         p.algo = use ? 1 : 0;
     }
     if (p.algo == 1) {
-        p.strip_slots = kStripSlots;
-        p.strip_smem = (size_t)kStripSlots * kChunkBytes + 128 + 2 * kStripSlots * sizeof(uint64_t);
+        {
+            const char* se = std::getenv("B2C_STRIP_SLOTS");
+            const int s = se ? std::atoi(se) : kStripSlots;
+            p.strip_slots = ((s >= 3 && s <= 6) || s == 8 || s == 10) ? s : 12;
+        }
+        p.strip_smem = (size_t)p.strip_slots * kChunkBytes + 128 + 2 * p.strip_slots * sizeof(uint64_t);
         std::vector<Segment> segs;
         std::vector<int> begin;
         build_strip_partition(p, p.strip_grid, segs, begin);
