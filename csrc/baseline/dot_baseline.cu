@@ -58,6 +58,18 @@ __global__ void dot_partials_kernel(const T* a, const T* b, int64_t n, T* out) {
     if (threadIdx.x == 0) out[blockIdx.x] = r;
 }
 
+// The reference's DEMONSTRATION of a data race (ref_parallel-dot-product-atomics.cu:26-32,
+// -DNO_SYNC): every block adds its partial to the scalar with a plain read-modify-write
+// instead of atomicAdd, so concurrent blocks lose updates and the result comes out too
+// small.  Kept as variant 3 for the same teaching purpose (and as a target for
+// `compute-sanitizer --tool racecheck`); never used by the product.
+template <typename T>
+__global__ void dot_racy_kernel(const T* a, const T* b, int64_t n, T* out) {
+    __shared__ T cache[kBlock];
+    T r = block_tree(strided_dot(a, b, n), cache);
+    if (threadIdx.x == 0) *reinterpret_cast<volatile T*>(out) = *reinterpret_cast<volatile T*>(out) + r;
+}
+
 __device__ unsigned int g_count = 0;
 
 template <typename T>
@@ -87,6 +99,9 @@ void launch(int variant, const T* a, const T* b, int64_t n, T* out, int blocks, 
         dot_atomic_kernel<T><<<blocks, kBlock, 0, st>>>(a, b, n, out);
     } else if (variant == 1) {
         dot_partials_kernel<T><<<blocks, kBlock, 0, st>>>(a, b, n, out);
+    } else if (variant == 3) {
+        cudaMemsetAsync(out, 0, sizeof(T), st);
+        dot_racy_kernel<T><<<blocks, kBlock, 0, st>>>(a, b, n, out);
     } else {
         dot_lastblock_kernel<T><<<blocks, kBlock, 0, st>>>(a, b, n, out);
     }
@@ -110,7 +125,7 @@ B2C_EXPORT int b2c_baseline_dot(int variant, const void* a, const void* b, int64
                                 void* out, void* stream) {
     B2C_TRY
     using namespace b200;
-    B200_REQUIRE(variant >= 0 && variant <= 2, ERR_ARG, "variant must be 0, 1 or 2");
+    B200_REQUIRE(variant >= 0 && variant <= 3, ERR_ARG, "variant must be 0, 1, 2 or 3 (racy demo)");
     B200_REQUIRE(dtype == 8 || dtype == 9, ERR_TYPE, "float32 or float64 only");
     const int blocks = b2c_baseline_dot_blocks(n);
     if (dtype == 9)

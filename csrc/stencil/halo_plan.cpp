@@ -83,31 +83,49 @@ Datatype make_subarray_type(const Array2D& g, const Array2D& sub, const Datatype
     return t;
 }
 
+TransferInfo make_recv_info(const comm::Comm& cart, GridCellID remote_source, RegionID local_target,
+                            const Array2D& tile, int stencilWidth, int stencilHeight, int tag,
+                            const Datatype& elem) {
+    int dx, dy;
+    cell_offset(remote_source, &dx, &dy);
+    TransferInfo r;
+    r.region = local_target;
+    r.layout = sub_array_region(tile, stencilWidth, stencilHeight, local_target);
+    r.type = make_subarray_type(tile, r.layout, elem);
+    r.peer = offset_rank(cart, dx, dy);
+    r.tag = tag;
+    return r;
+}
+
+TransferInfo make_send_info(const comm::Comm& cart, GridCellID remote_target, RegionID local_source,
+                            const Array2D& tile, int stencilWidth, int stencilHeight, int tag,
+                            const Datatype& elem) {
+    int dx, dy;
+    cell_offset(remote_target, &dx, &dy);
+    const Array2D core_l = sub_array_region(tile, stencilWidth, stencilHeight, CENTER);
+    TransferInfo s;
+    s.region = local_source;
+    s.layout = sub_array_region(core_l, stencilWidth, stencilHeight, local_source);
+    s.type = make_subarray_type(tile, s.layout, elem);
+    s.peer = offset_rank(cart, dx, dy);
+    s.tag = tag;
+    return s;
+}
+
 HaloPlan::HaloPlan(const comm::Comm& cart, const Array2D& tile, int stencilWidth,
                    int stencilHeight, const Datatype& elem)
     : cart_(cart), tile_(tile), sw_(stencilWidth), sh_(stencilHeight) {
     B200_REQUIRE(cart.is_cart(), ERR_TOPOLOGY, "halo plan needs a Cartesian communicator");
-    const Array2D core_l = core();
     for (int c = 0; c < NUM_CELLS; ++c) {
-        int dx, dy;
-        cell_offset((GridCellID)c, &dx, &dy);
-        // send: the slice of my core that faces neighbour c, to neighbour c
-        TransferInfo s;
-        s.region = kSendRegion[c];
-        s.layout = sub_array_region(core_l, sw_, sh_, s.region);
-        s.type = make_subarray_type(tile_, s.layout, elem);
-        s.peer = offset_rank(cart, dx, dy);
-        s.tag = (int)s.region;
-        send_.push_back(s);
-        // receive: my ghost cells on the OPPOSITE side, from the neighbour there;
-        // that neighbour sends the region facing direction c, hence the same tag
-        TransferInfo r;
-        r.region = kGhostRegion[NUM_CELLS - 1 - c];
-        r.layout = sub_array_region(tile_, sw_, sh_, r.region);
-        r.type = make_subarray_type(tile_, r.layout, elem);
-        r.peer = offset_rank(cart, -dx, -dy);
-        r.tag = (int)s.region;
-        recv_.push_back(r);
+        // send: the slice of my core that faces neighbour c, to neighbour c; the tag is
+        // the id of the send region
+        const RegionID sreg = kSendRegion[c];
+        send_.push_back(make_send_info(cart, (GridCellID)c, sreg, tile_, sw_, sh_, (int)sreg, elem));
+        // receive: my ghost cells on the OPPOSITE side, from the neighbour there; that
+        // neighbour sends the region facing direction c, hence the same tag
+        const int opp = NUM_CELLS - 1 - c;
+        recv_.push_back(make_recv_info(cart, (GridCellID)opp, kGhostRegion[opp], tile_, sw_, sh_,
+                                       (int)sreg, elem));
     }
 }
 

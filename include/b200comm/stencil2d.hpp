@@ -81,6 +81,18 @@ void cell_offset(GridCellID c, int* dx, int* dy);
 // dimension 0 is the row axis; PROC_NULL outside a non-periodic grid.
 int offset_rank(const comm::Comm& cart, int dx, int dy);
 
+// Customisation point: the datatype of one array element.  The reference declares
+// CreateArrayElementType<T>() and lets client code specialise it (stencil2D.h:206,
+// mpi-2d-stencil-subarray.cpp:10 for double); here the arithmetic types are provided
+// and user types are added by specialising this template the same way.
+template <typename T> Datatype element_type();
+template <> inline Datatype element_type<double>() { return Datatype::basic(Basic::DOUBLE); }
+template <> inline Datatype element_type<float>() { return Datatype::basic(Basic::FLOAT); }
+template <> inline Datatype element_type<int>() { return Datatype::basic(Basic::INT32); }
+template <> inline Datatype element_type<long long>() { return Datatype::basic(Basic::INT64); }
+template <> inline Datatype element_type<char>() { return Datatype::basic(Basic::CHAR); }
+template <> inline Datatype element_type<unsigned char>() { return Datatype::basic(Basic::UINT8); }
+
 // Subarray datatype selecting `sub` inside the allocation that `g` describes.
 Datatype make_subarray_type(const Array2D& g, const Array2D& sub, const Datatype& elem);
 
@@ -91,6 +103,17 @@ struct TransferInfo {
     Array2D layout;               // the region inside the tile allocation
     Datatype type;                // committed subarray type
 };
+
+// One entry of the plan (CreateReceiveInfo / CreateSendInfo, stencil2D.h:319-359):
+// `make_recv_info` describes ghost region `local_target` of the full tile, filled by the
+// neighbour in direction `remote_source`; `make_send_info` describes region `local_source`
+// of the CORE, sent to the neighbour in direction `remote_target`.
+TransferInfo make_recv_info(const comm::Comm& cart, GridCellID remote_source, RegionID local_target,
+                            const Array2D& tile, int stencilWidth, int stencilHeight, int tag,
+                            const Datatype& elem);
+TransferInfo make_send_info(const comm::Comm& cart, GridCellID remote_target, RegionID local_source,
+                            const Array2D& tile, int stencilWidth, int stencilHeight, int tag,
+                            const Datatype& elem);
 
 // The 8 (send, receive) pairs of one halo exchange.  Tag = id of the SEND
 // region, so messages stay distinct even when several directions map to the

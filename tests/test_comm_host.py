@@ -309,3 +309,21 @@ def test_invalid_arguments():
             codes.append(ei.value.code)
         return codes
     assert cm.run_local(1, body)[0] == [7, 5, 9, 9]   # RANK, TAG, TOPOLOGY, TOPOLOGY
+
+
+def test_rank_utilities_node_count_elapsed_block_range(capsys):
+    from cuda_mpi_scratch_b200.utils import ranks as ru
+
+    def body(c):
+        t0 = cm.wtime()
+        n = ru.node_count(c)
+        el = ru.global_elapsed(c, t0 - 0.001 * c.rank, cm.wtime())
+        ru.rank_print(c, "nodes", n)
+        return n, el > 0.0, ru.block_range(1 << 10, c.rank, c.size)
+    out = cm.run_local(4, body)
+    assert all(o[0] == 1 and o[1] for o in out)
+    assert [o[2] for o in out] == [(256 * r, 256 * (r + 1)) for r in range(4)]
+    lines = [l for l in capsys.readouterr().out.splitlines() if "nodes 1" in l]
+    assert len(lines) == 4 and all(" - rank " in l for l in lines)
+    with pytest.raises(ValueError):
+        ru.block_range(10, 0, 3)
