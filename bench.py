@@ -36,6 +36,8 @@ def parse_args(argv=None):
     ap.add_argument("--tile", type=int, default=16384, help="cells per side of each GPU's tile")
     ap.add_argument("--radius", type=int, default=1)
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--th", type=int, default=0, help="explicit per-GPU tile height (experiments)")
+    ap.add_argument("--tw", type=int, default=0, help="explicit per-GPU tile width (experiments)")
     return ap.parse_args(argv)
 
 
@@ -74,6 +76,8 @@ def main(argv=None) -> int:
         th = tw = args.tile
     else:  # strong: total work fixed at tile^2, split over the grid
         th, tw = args.tile // dims[0], args.tile // dims[1]
+    if args.th and args.tw:
+        th, tw = args.th, args.tw
     R = args.radius
     st = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True)
     dev = st.device

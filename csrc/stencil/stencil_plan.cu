@@ -216,18 +216,23 @@ struct Plan {
 // possible: every CTA then owns one long segment and all CTAs of a band advance together.
 static int choose_strip_width(int W, int H, int R, int G) {
     const int wmax = std::min(kStripW, W);
-    int best_w = wmax & ~1, best_busy = -1;
+    int best_w = wmax & ~1;
+    long best_score = -1;
     const int CY = (H + kChunkH - 1) / kChunkH;
-    for (int NB = 1; NB <= 16; ++NB) {
-        const int NSi = G / NB;
-        if (NSi < 1 || CY - 2 < 8 * NB) continue;
-        int sw = ((W + (NSi + 2) - 1) / (NSi + 2) + 1) & ~1;     // ceil(W / NS), rounded up to even
-        if (sw > wmax || sw < 64) continue;
+    // Score = busy CTAs x strip width: narrow strips waste lanes, TMA efficiency and
+    // sectors (68-cell strips on a 4096-wide tile ran at half the speed of 200-cell ones).
+    // Evaluate every even width exactly the way build_strip_partition will use it.
+    for (int sw = 32; sw <= (wmax & ~1); sw += 2) {
         const int NS = (W + sw - 1) / sw;
         const int last = W - (NS - 1) * sw;
         if (NS < 3 || (last != sw && last < R)) continue;
-        const int busy = std::min(NS - 2, NSi) * NB;
-        if (busy > best_busy || (busy == best_busy && sw > best_w)) { best_busy = busy; best_w = sw; }
+        const int NSi = NS - 2;
+        const int NB = G / NSi;                       // row bands the partition will make
+        if (NB < 1 || CY - 2 < 8 * NB) continue;
+        // busy CTAs x per-CTA efficiency; the +40 models the fixed cost per chunk row
+        // (halo columns, sector rounding, barrier traffic) in units of cells
+        const long score = (long)NSi * NB * 1000L * sw / (sw + 40);
+        if (score >= best_score) { best_score = score; best_w = sw; }
     }
     return best_w;
 }
@@ -524,7 +529,11 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         const bool eligible = kind == 0 && R <= 2 &&
                               (W % p.strip_w == 0 || W % p.strip_w >= R) &&
                               (H % kChunkH == 0 || H % kChunkH >= R);
-        bool use = eligible;
+        // Measured cross-over (profiles/stencil_strip_sweeps.txt): the strip kernel wins on
+        // 16384^2 cells per GPU (365 vs 341 Gcell/s), ties at 16384 x 8192 and loses below
+        // (long sequential segments pay their pipeline fill; 4096^2: 240 vs 308).
+        bool use = eligible && (long)W * H >= 200000000L;
+        if (ae && std::string(ae) == "strip") use = eligible;
         if (ae && std::string(ae) == "tile") use = false;
         if (ae && std::string(ae) == "strip")
             B200_REQUIRE(eligible, ERR_ARG, "strip kernel not applicable to this stencil/tile");
