@@ -45,10 +45,13 @@ namespace b200 {
 namespace stencil {
 
 constexpr int kTileW = 128;        // output cells per tile row (1 KiB of fp64)
-constexpr int kTileH = 32;         // output rows per tile
+#ifndef B2C_TILE_H
+#define B2C_TILE_H 32
+#endif
+constexpr int kTileH = B2C_TILE_H;         // output rows per tile
 constexpr int kConsumers = 256;    // 8 consumer warps
 constexpr int kThreads = kConsumers + 32;  // + 1 producer warp
-constexpr int kRowsPerThread = 8;  // 4 row bands x 8 rows, 64 column pairs
+constexpr int kRowsPerThread = kTileH / 4;  // 4 row bands, 64 column pairs
 constexpr int kMaxRadius = 4;
 
 // Neighbour directions, numbered like the reference's MPIGridCellID

@@ -391,6 +391,11 @@ static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) 
 template <int R, bool BOX>
 static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
     constexpr int NST = R <= 2 ? 3 : 4;
+    if (R <= 2 && pl.nstages == 2) {   // shallower ring (B2C_TILE_STAGES=2), see DESIGN.md
+        if (resid) launch_one<R, BOX, true, 2>(pl, lp, st);
+        else launch_one<R, BOX, false, 2>(pl, lp, st);
+        return;
+    }
     if (resid) launch_one<R, BOX, true, NST>(pl, lp, st);
     else launch_one<R, BOX, false, NST>(pl, lp, st);
 }
@@ -488,6 +493,21 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
     const size_t stage = (((size_t)(kTileW + 2 * RA) * (kTileH + 2 * R) * 8) + 127) & ~(size_t)127;
     p.nstages = R <= 2 ? 3 : 4;
     p.ctas_per_sm = R <= 2 ? 2 : 1;
+    {
+        // How much to keep in flight is THE tuning parameter of this kernel on B200
+        // (profiles/README.md): with many tiles per SM, one CTA per SM and a 2-stage ring
+        // (36-72 KB in flight per SM ~ HBM latency x bandwidth) runs at copy-level DRAM
+        // efficiency (16384^2: 370 vs 340 Gcell/s with 2 CTAs x 3 stages); with few tiles per
+        // SM the deeper, wider configuration hides the start-up better (4096^2: 310 vs 296).
+        cudaDeviceProp pr;
+        B200_CHECK_CUDA(cudaGetDeviceProperties(&pr, p.device));
+        const long tiles_per_sm = (long)p.tilesX * p.tilesY / std::max(1, pr.multiProcessorCount);
+        if (R <= 2 && tiles_per_sm >= 64) { p.nstages = 2; p.ctas_per_sm = 1; }
+    }
+    if (const char* te = std::getenv("B2C_TILE_STAGES"))
+        if (R <= 2 && (std::atoi(te) == 2 || std::atoi(te) == 3)) p.nstages = std::atoi(te);
+    if (const char* ce = std::getenv("B2C_TILE_CTAS_PER_SM"))
+        if (R <= 2 && (std::atoi(ce) == 1 || std::atoi(ce) == 2)) p.ctas_per_sm = std::atoi(ce);
     p.smem = p.nstages * stage + 2 * p.nstages * sizeof(uint64_t);
     cudaDeviceProp prop;
     B200_CHECK_CUDA(cudaGetDeviceProperties(&prop, p.device));
@@ -529,10 +549,12 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         const bool eligible = kind == 0 && R <= 2 &&
                               (W % p.strip_w == 0 || W % p.strip_w >= R) &&
                               (H % kChunkH == 0 || H % kChunkH >= R);
-        // Measured cross-over (profiles/stencil_strip_sweeps.txt): the strip kernel wins on
-        // 16384^2 cells per GPU (365 vs 341 Gcell/s), ties at 16384 x 8192 and loses below
-        // (long sequential segments pay their pipeline fill; 4096^2: 240 vs 308).
-        bool use = eligible && (long)W * H >= 200000000L;
+        // Measured (profiles/stencil_strip_sweeps.txt): with its ring depth tuned the tile
+        // kernel ties the strip kernel on 16384^2 cells per GPU (369 vs 365-368 Gcell/s on one
+        // GPU, 716 vs 716 on two) and wins on every smaller tile (4096^2: 308 vs 240; long
+        // sequential segments pay their pipeline fill), so the tile kernel is the default and
+        // the strip kernel (6 % less DRAM traffic) is opt-in: B2C_STENCIL_ALGO=strip.
+        bool use = false;
         if (ae && std::string(ae) == "strip") use = eligible;
         if (ae && std::string(ae) == "tile") use = false;
         if (ae && std::string(ae) == "strip")

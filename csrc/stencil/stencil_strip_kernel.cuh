@@ -31,7 +31,7 @@ namespace stencil {
 
 constexpr int kStripW = 252;          // MAX cells per strip (box = 252 + 2*2 = 256 columns); the
                                       // actual width is chosen per plan so that bands x strips = CTAs
-constexpr int kChunkH = 4;            // rows per TMA chunk (8 KiB); 6 slots -> 4 CTAs per SM
+constexpr int kChunkH = 4;            // rows per TMA chunk (2 and 8 measured slower, see profiles/)
 constexpr int kStripCtasPerSm = 4;
 constexpr int kStripBoxW = 256;
 constexpr int kStripConsumers = 128;  // 4 consumer warps, 2 columns per thread

@@ -47,6 +47,7 @@ NVCC_FLAGS = ARCH_FLAGS + [
     "--expt-relaxed-constexpr",
     f"-I{INCLUDE}", f"-I{CSRC}",
 ]
+NVCC_FLAGS += os.environ.get("B200COMM_NVCC_EXTRA", "").split()   # e.g. -DB2C_TILE_H=64 (experiments)
 CXX_FLAGS = [
     "-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-pthread",
     f"-I{INCLUDE}", f"-I{CSRC}", f"-I{CUDA_HOME / 'include'}",
