@@ -111,10 +111,14 @@ def main(argv=None) -> int:
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
     world.barrier()
+    if sampler is not None:
+        sampler.window_begin()
     e0.record(stream)
     st.step(args.steps)
     e1.record(stream)
     torch.cuda.synchronize(dev)
+    if sampler is not None:
+        sampler.window_end()
     world.barrier()
     ms = e0.elapsed_time(e1)
     launches = st.kernel_launches - launches0
@@ -134,6 +138,8 @@ def main(argv=None) -> int:
         stream.synchronize()
     world.barrier()
     torch.cuda.synchronize(dev)
+    if sampler is not None:
+        sampler.window_begin()
     t0 = time.perf_counter()
     res = 0.0
     for _ in range(args.steps):
@@ -144,6 +150,8 @@ def main(argv=None) -> int:
         res = float(buf.item())
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
+    if sampler is not None:
+        sampler.window_end()
     e2e_s = world.allreduce_max(e2e_s)
     clocks = sampler.stop() if sampler is not None else None
     st.check()

@@ -63,7 +63,53 @@ class ClockSampler:
         self._proc: subprocess.Popen | None = None
         self._thr: threading.Thread | None = None
 
+    # NVML bit masks of nvmlDeviceGetCurrentClocksEventReasons
+    _NVML_REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+                     0x40: "hw_thermal_slowdown"}
+
+    def _start_nvml(self) -> bool:
+        """Poll NVML in-process every ~2 ms: dozens of samples even for a 20 ms timed region."""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self._nvml_index())
+            smax = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            return False
+        self._stop_evt = threading.Event()
+
+        def pump():
+            import time
+            while not self._stop_evt.is_set():
+                try:
+                    sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                    pw = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                    try:
+                        mask = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    except Exception:
+                        mask = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    flags = ["Active" if mask & b else "Not Active" for b in (0x8, 0x40, 0x20, 0x4)]
+                    self.rows.append([str(self.device), str(sm), str(smax), f"{pw:.2f}", hex(mask)] + flags)
+                except Exception:
+                    pass
+                time.sleep(0.002)
+
+        self._thr = threading.Thread(target=pump, daemon=True)
+        self._thr.start()
+        self.source = "nvml"
+        return True
+
+    def _nvml_index(self) -> int:
+        """NVML enumerates physical GPUs; honour CUDA_VISIBLE_DEVICES when it lists indices."""
+        import os
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        ids = [v for v in vis.split(",") if v.strip().isdigit()]
+        return int(ids[self.device]) if self.device < len(ids) else self.device
+
     def start(self) -> "ClockSampler":
+        self.source = "nvidia-smi"
+        if self._start_nvml():
+            return self
         try:
             self._proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={_QUERY}", "--format=csv,noheader,nounits",
@@ -91,6 +137,8 @@ class ClockSampler:
                 self.rows.append(parts)
 
     def stop(self) -> dict:
+        if getattr(self, "_stop_evt", None) is not None:
+            self._stop_evt.set()
         if self._proc is not None:
             self._proc.terminate()
             try:
@@ -101,11 +149,25 @@ class ClockSampler:
             self._thr.join(timeout=2)
         return self.summary()
 
+    def window_begin(self) -> None:
+        """Mark the start of a timed region: only samples inside windows are summarised."""
+        self._windows = getattr(self, "_windows", [])
+        self._windows.append([len(self.rows), None])
+
+    def window_end(self) -> None:
+        if getattr(self, "_windows", None) and self._windows[-1][1] is None:
+            self._windows[-1][1] = len(self.rows)
+
     def summary(self) -> dict:
         sm, smax, power = [], [], []
         reasons: set[str] = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = self.rows
+        wins = [w for w in getattr(self, "_windows", []) if w[1] is not None and w[1] > w[0]]
+        in_window = bool(wins)
+        if in_window:
+            rows = [r for a, b in wins for r in self.rows[a:b]]
+        for r in rows:
             try:
                 sm.append(float(r[1]))
                 smax.append(float(r[2]))
@@ -117,9 +179,11 @@ class ClockSampler:
                     reasons.add(name)
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        # "under load": samples in the upper half of the power range
-        pmid = (max(power) + min(power)) / 2
-        load = [s for s, p in zip(sm, power) if p >= pmid] or sm
+        if in_window:
+            load = sm      # every sample was taken inside a timed region
+        else:              # "under load": samples in the upper half of the power range
+            pmid = (max(power) + min(power)) / 2
+            load = [s for s, p in zip(sm, power) if p >= pmid] or sm
         return {"sm_mhz": statistics.median(load), "sm_max_mhz": max(smax),
-                "reasons": sorted(reasons), "samples": len(sm),
-                "power_w_max": max(power)}
+                "reasons": sorted(reasons), "samples": len(sm), "samples_in_timed_regions": in_window,
+                "power_w_max": max(power), "source": getattr(self, "source", "nvidia-smi")}
