@@ -253,6 +253,32 @@ class Stencil2D:
         t = self.tile.cpu()
         return "".join("".join(fmt.format(v) + " " for v in row.tolist()) + "\n" for row in t)
 
+    def set_timeout_ms(self, ms: int) -> None:
+        """Deadline of every device-side flag wait (default 20 s).  When a neighbour never
+        delivers, the wait gives up, a status bit is set and :meth:`check` raises."""
+        _lib.check(_lib.lib.b2c_stencil_set_timeout_ms(self._h, int(ms)))
+
+    # ------------------------------------------------------------ checkpoint / resume
+    def save_checkpoint(self, path: str) -> None:
+        """Write this rank's state (core cells, ghost cells, step count, geometry) to ``path``.
+        The reference has no checkpointing, only the per-rank text dump
+        (``mpi-2d-stencil-subarray-cuda.cu:114-119,164-176``); this is the binary form of it."""
+        torch.cuda.current_stream(self.device).synchronize()
+        torch.save({"tile": self.tile.cpu(), "steps_done": int(self.info().steps_done),
+                    "rank": self.rank, "dims": self.cart.dims, "periods": self.cart.periods,
+                    "tile_hw": (self.H, self.W), "radius": self.radius, "kind": self.kind}, path)
+
+    def load_checkpoint(self, path: str) -> int:
+        """Restore the state saved by :meth:`save_checkpoint` into the CURRENT buffer (core and
+        ghost cells) and return the step count of the checkpoint.  Call :meth:`exchange`
+        afterwards (collective) before stepping again."""
+        ck = torch.load(path)
+        if tuple(ck["tile_hw"]) != (self.H, self.W) or ck["radius"] != self.radius or ck["rank"] != self.rank:
+            raise ValueError("checkpoint does not match this plan (tile size, radius or rank)")
+        self.tile.copy_(ck["tile"].to(self.tile.device))
+        torch.cuda.current_stream(self.device).synchronize()
+        return int(ck["steps_done"])
+
     def close(self) -> None:
         if self._h:
             _lib.lib.b2c_stencil_destroy(self._h)

@@ -138,6 +138,42 @@ def test_both_kernels_agree_bitwise_and_match_oracle(monkeypatch, algo, dims, ti
     assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
 
 
+def test_missing_neighbour_times_out_instead_of_hanging():
+    """Failure detection: if a neighbour never delivers its halo, the device-side wait gives
+    up after its deadline, sets the status word, and check() raises ERR_TIMEOUT."""
+    grp = Stencil2D.create_group(cms.LocalGroup(2), (32, 128), 1, "star", dims=(1, 2))
+    for s in grp.ranks:
+        s.fill(1.0, 1.0)
+        s.set_timeout_ms(30)
+    grp.exchange()
+    a = grp.ranks[0]
+    a.step(1, drain=False)        # fine: step 0 needs no epochs
+    a.step(1, drain=False)        # needs rank 1's step-0 halo, which is never produced
+    with pytest.raises(cms.CommError) as ei:
+        a.check()
+    assert ei.value.code == 11    # ERR_TIMEOUT
+
+
+def test_checkpoint_resume_continues_bit_identically(tmp_path):
+    dims, hw = (2, 2), (64, 256)
+    grp, glob = _run_group(dims, hw, 1, "star", 3)
+    for s in grp.ranks:
+        s.save_checkpoint(str(tmp_path / f"ck{s.rank}.pt"))
+    grp.step(4)
+    grp.sync()
+    want = grp.gather_global()
+    # fresh plans, restored from the files, must reproduce the same continuation
+    grp2 = Stencil2D.create_group(cms.LocalGroup(4), hw, 1, "star", dims=dims)
+    for s in grp2.ranks:
+        s.fill(0.0, 0.0)
+        assert s.load_checkpoint(str(tmp_path / f"ck{s.rank}.pt")) == 3
+    grp2.exchange()
+    grp2.step(4)
+    grp2.sync()
+    grp2.check()
+    assert torch.equal(grp2.gather_global(), want)
+
+
 def test_exchange_reproduces_reference_golden_layout():
     """3x3 periodic grid, 16x16 tile, 5x5 stencil (ghost 2), core = rank id, ghosts = -1:
     after ONE device-side exchange every ghost block holds the id of the neighbour on

@@ -1,0 +1,33 @@
+"""Host-side utilities that must work (or degrade quietly) on a box without GPUs."""
+import os
+import subprocess
+import sys
+
+from cuda_mpi_scratch_b200.utils.timing import ClockSampler
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_clock_sampler_without_gpu_reports_no_samples():
+    s = ClockSampler(0, period_ms=20).start()
+    s.wait_first(0.2)
+    s.window_begin()
+    s.window_end()
+    out = s.stop()
+    assert out["samples"] == 0 and out["sm_mhz"] is None and out["reasons"] == []
+
+
+def test_reference_arm_reports_unavailable():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference"],
+                         check=True, capture_output=True, text=True, timeout=120).stdout
+    assert '"impl": "reference"' in out and '"unavailable"' in out
+
+
+def test_launcher_propagates_failure(tmp_path):
+    prog = tmp_path / "boom.py"
+    prog.write_text("import os, sys, time\n"
+                    "r = int(os.environ['B200_RANK'])\n"
+                    "sys.exit(3) if r == 1 else time.sleep(30)\n")
+    p = subprocess.run([sys.executable, "-m", "cuda_mpi_scratch_b200.launch", "-n", "3", str(prog)],
+                       cwd=ROOT, timeout=60)
+    assert p.returncode == 3      # the failing rank's code; the sleeping ranks were terminated
