@@ -89,7 +89,13 @@ struct LaunchParams {
     const double* my_land[2];  // my west / east column landing buffers (in parity)
     uint64_t* peer_flag[8];    // neighbour's epoch counter that I bump per direction
     const uint64_t* my_flags;  // my 8 epoch counters (indexed by the direction data comes from)
-    uint64_t wait_epoch[8];    // value my_flags[d] must reach before ghost cells of d are read
+    // my_flags[d] must reach (*step_ctr + step_off) * signals_per_step[d] before the ghost
+    // cells of direction d are read.  The step count lives in DEVICE memory (bumped by a
+    // one-thread kernel after each batch of steps) so that a captured CUDA graph of N
+    // steps can be replayed: its kernel parameters never change, the counter does.
+    const uint64_t* step_ctr;
+    uint64_t step_off;
+    uint64_t signals_per_step[8];
     double* resid_partials;    // [gridDim.x] per-CTA sum of (out-in)^2, or nullptr
     unsigned int* status;      // device status word (bit0: flag wait timed out)
     uint64_t timeout_ns;       // spin deadline per wait
@@ -191,7 +197,8 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                     for (int d = 0; d < 8; ++d) {
                         if (!(act >> d & 1u)) continue;
                         uint32_t spins = 0;
-                        while (ptx::ld_acquire_sys(P.my_flags + d) < P.wait_epoch[d]) {
+                        const uint64_t need = (*P.step_ctr + P.step_off) * P.signals_per_step[d];
+                        while (ptx::ld_acquire_sys(P.my_flags + d) < need) {
                             if ((++spins & 1023u) == 0 &&
                                 ptx::globaltimer_ns() - t0 > P.timeout_ns) {
                                 atomicOr(P.status, 1u);

@@ -32,6 +32,7 @@ constexpr size_t kPadBytes = 4096;
 constexpr size_t kOffStepFlags = 0;     // 8 x u64: fused-step epoch counters
 constexpr size_t kOffXchgFlags = 64;    // 8 x u64: unfused-exchange epoch counters
 constexpr size_t kOffStatus = 128;      // u32 status word
+constexpr size_t kOffStepCtr = 192;     // u64: fused steps completed (device-side mirror)
 constexpr size_t kOffResid = 256;       // double: last local residual (sum of squares)
 constexpr size_t kOffRedSlots = 1024;   // scalar allreduce slots (see collectives)
 
@@ -122,8 +123,9 @@ __global__ void land_unpack_kernel(const __grid_constant__ UnpackParams P) {
 }
 
 struct WaitParams {
-    const uint64_t* flags;   // 8 counters
-    uint64_t epoch[8];       // required values (0: do not wait)
+    const uint64_t* flags;     // 8 counters
+    uint64_t epoch[8];         // required values (0: do not wait); multiplied by *step_ctr if set
+    const uint64_t* step_ctr;  // device step counter or nullptr
     unsigned int* status;
     uint64_t timeout_ns;
 };
@@ -133,15 +135,18 @@ struct WaitParams {
 __global__ void flag_wait_kernel(const __grid_constant__ WaitParams P) {
     const int d = threadIdx.x;
     if (d >= 8 || P.epoch[d] == 0) return;
+    const uint64_t need = P.step_ctr ? (*P.step_ctr) * P.epoch[d] : P.epoch[d];
     const uint64_t t0 = ptx::globaltimer_ns();
     uint32_t spins = 0;
-    while (ptx::ld_acquire_sys(P.flags + d) < P.epoch[d]) {
+    while (ptx::ld_acquire_sys(P.flags + d) < need) {
         if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
             atomicOr(P.status, 1u);
             break;
         }
     }
 }
+
+__global__ void step_bump_kernel(uint64_t* ctr, uint64_t n) { *ctr += n; }
 
 __global__ void sum_partials_kernel(const double* __restrict__ partials, int n, double* out) {
     __shared__ double sh[256];
@@ -202,6 +207,7 @@ struct Plan {
     uint64_t timeout_ns;
     int tilesX, tilesY;
     uint64_t contrib[8];         // signals per step a neighbour sends me per direction
+    unsigned long long launches; // kernels launched through this plan (for bench accounting)
     // ---- strip kernel (algo 1) ----
     int algo;                    // 0 tile kernel, 1 strip kernel
     CUtensorMap strip_tmap[2];
@@ -642,22 +648,26 @@ B2C_EXPORT int b2c_stencil_info(b2c_stencil* h, b2c_stencil_info_t* o) {
     o->ncoef = p.ncoef; o->launches_per_step = 1;
     o->buf[0] = p.base + p.L.off_x[0]; o->buf[1] = p.base + p.L.off_x[1];
     o->resid = reinterpret_cast<double*>(p.base + kOffResid);
+    o->launches = p.launches;
     B2C_CATCH
 }
 
-static void drain_impl(Plan& p, bool xchg, cudaStream_t st) {
+static int drain_impl(Plan& p, bool xchg, cudaStream_t st) {
     WaitParams wp{};
     wp.flags = reinterpret_cast<const uint64_t*>(p.base + (xchg ? kOffXchgFlags : kOffStepFlags));
     wp.status = reinterpret_cast<unsigned*>(p.base + kOffStatus);
     wp.timeout_ns = p.timeout_ns;
     bool any = false;
+    // fused steps: the kernel multiplies the DEVICE step counter (graph replays advance it);
+    // unfused exchanges: plain host-side epochs
+    wp.step_ctr = xchg ? nullptr : reinterpret_cast<const uint64_t*>(p.base + kOffStepCtr);
     for (int d = 0; d < 8; ++d) {
         wp.epoch[d] = 0;
         if (!dir_active(p, d)) continue;
-        wp.epoch[d] = xchg ? p.xchg_done : p.steps_done * contributions(p, d);
+        wp.epoch[d] = xchg ? p.xchg_done : (p.steps_done ? contributions(p, d) : 0);
         any = any || wp.epoch[d] != 0;
     }
-    if (!any) return;
+    if (!any) return 0;
     flag_wait_kernel<<<1, 32, 0, st>>>(wp);
     B200_CHECK_LAUNCH();
     // refresh the in-grid ghost columns of the current buffer from the landing buffers
@@ -670,11 +680,12 @@ static void drain_impl(Plan& p, bool xchg, cudaStream_t st) {
         up.active[d] = dir_active(p, d) && dir_dx(d) != 0 && wp.epoch[d] != 0;
         cols = cols || up.active[d];
     }
-    if (!cols) return;
+    if (!cols) return 1;
     up.W = p.L.W; up.H = p.L.H; up.g = p.L.g; up.lead = p.L.lead; up.pitch = p.L.pitch;
     const int n = 2 * p.L.rows * p.L.g;
     land_unpack_kernel<<<(n + 255) / 256 > 64 ? 64 : (n + 255) / 256, 256, 0, st>>>(up);
     B200_CHECK_LAUNCH();
+    return 2;
 }
 
 // Launch `nsteps` fused steps.  flags: bit0 = compute the residual of the LAST
@@ -704,12 +715,17 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
                     reinterpret_cast<double*>(p.nbr[d] + p.L.off_land[outb][dir_dx(d) < 0 ? 1 : 0]);
                 lp.peer_flag[d] =
                     reinterpret_cast<uint64_t*>(p.nbr[d] + kOffStepFlags) + dir_opposite(d);
-                lp.wait_epoch[d] = p.steps_done * contributions(p, d);
+                lp.signals_per_step[d] = contributions(p, d);
             } else {
                 lp.peer_out[d] = nullptr; lp.peer_land[d] = nullptr; lp.peer_flag[d] = nullptr;
-                lp.wait_epoch[d] = 0;
+                lp.signals_per_step[d] = 0;
             }
         }
+        // epochs are derived on the device from the step counter in the pad (+ the offset of
+        // this step inside the batch), so the same launch parameters work for every replay of
+        // a captured graph
+        lp.step_ctr = reinterpret_cast<const uint64_t*>(p.base + kOffStepCtr);
+        lp.step_off = (uint64_t)s;
         lp.my_land[0] = reinterpret_cast<const double*>(p.base + p.L.off_land[in][0]);
         lp.my_land[1] = reinterpret_cast<const double*>(p.base + p.L.off_land[in][1]);
         lp.W = p.L.W; lp.H = p.L.H; lp.g = p.L.g; lp.lead = p.L.lead; lp.pitch = p.L.pitch;
@@ -717,22 +733,40 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         { const char* dbg = std::getenv("B2C_STENCIL_DEBUG"); lp.debug = dbg ? std::atoi(dbg) : 0; }
         const bool resid = (flags & 1) && s == nsteps - 1;
         launch_step(p, lp, resid, st);
+        p.launches += resid ? 2 : 1;
         if (resid) {
             sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials, p.algo == 1 ? p.strip_grid : p.grid,
                                                    reinterpret_cast<double*>(p.base + kOffResid));
             B200_CHECK_LAUNCH();
         }
         p.cur = outb;
-        p.steps_done += 1;
     }
-    if (flags & 2) drain_impl(p, false, st);
+    if (nsteps > 0) {
+        step_bump_kernel<<<1, 1, 0, st>>>(reinterpret_cast<uint64_t*>(p.base + kOffStepCtr), (uint64_t)nsteps);
+        B200_CHECK_LAUNCH();
+        p.steps_done += (uint64_t)nsteps;
+        p.launches += 1;
+    }
+    if (flags & 2) p.launches += drain_impl(p, false, st);
+    B2C_CATCH
+}
+
+// Host bookkeeping for replays of a captured graph of `nsteps` steps (the device-side
+// counter is advanced by the graph itself): moves the plan's step count and buffer parity.
+B2C_EXPORT int b2c_stencil_advance(b2c_stencil* h, long long nsteps) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    Plan& p = h->p;
+    B200_REQUIRE(nsteps >= 0 || (uint64_t)(-nsteps) <= p.steps_done, ERR_ARG, "cannot rewind past step 0");
+    p.steps_done = (uint64_t)((long long)p.steps_done + nsteps);
+    if (nsteps & 1) p.cur ^= 1;
     B2C_CATCH
 }
 
 B2C_EXPORT int b2c_stencil_drain(b2c_stencil* h, void* stream) {
     B2C_TRY
     B200_REQUIRE(h, ERR_ARG, "null plan");
-    drain_impl(h->p, false, (cudaStream_t)stream);
+    h->p.launches += drain_impl(h->p, false, (cudaStream_t)stream);
     B2C_CATCH
 }
 
@@ -755,6 +789,7 @@ B2C_EXPORT int b2c_stencil_exchange_push(b2c_stencil* h, void* stream) {
     }
     halo_push1_kernel<<<8, 512, 0, (cudaStream_t)stream>>>(xp);
     B200_CHECK_LAUNCH();
+    p.launches += 1;
     p.xchg_done += 1;
     B2C_CATCH
 }
@@ -763,7 +798,7 @@ B2C_EXPORT int b2c_stencil_exchange_push(b2c_stencil* h, void* stream) {
 B2C_EXPORT int b2c_stencil_exchange_wait(b2c_stencil* h, void* stream) {
     B2C_TRY
     B200_REQUIRE(h, ERR_ARG, "null plan");
-    drain_impl(h->p, true, (cudaStream_t)stream);
+    h->p.launches += drain_impl(h->p, true, (cudaStream_t)stream);
     B2C_CATCH
 }
 
@@ -779,6 +814,7 @@ B2C_EXPORT int b2c_stencil_fill(b2c_stencil* h, int which, int region, double va
     dim3 blk(64, 4), grd((w + 63) / 64, (hh + 3) / 4);
     fill_rect_kernel<<<grd, blk, 0, (cudaStream_t)stream>>>(b, p.L.pitch, x0, y0, w, hh, value);
     B200_CHECK_LAUNCH();
+    p.launches += 1;
     B2C_CATCH
 }
 

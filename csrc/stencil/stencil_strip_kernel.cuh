@@ -93,7 +93,8 @@ stencil_strip_kernel(const __grid_constant__ CUtensorMap tmap_in,
                     for (int d = 0; d < 8; ++d) {
                         if (!(act >> d & 1u)) continue;
                         uint32_t spins = 0;
-                        while (ptx::ld_acquire_sys(P.my_flags + d) < P.wait_epoch[d]) {
+                        const uint64_t need = (*P.step_ctr + P.step_off) * P.signals_per_step[d];
+                        while (ptx::ld_acquire_sys(P.my_flags + d) < need) {
                             if ((++spins & 1023u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
                                 atomicOr(P.status, 1u);
                                 break;

@@ -36,11 +36,32 @@ ERR_TIMEOUT = 11
 ERR_TRUNCATE = 8
 
 
-def _load() -> C.CDLL:
-    if not LIB_PATH.exists() or os.environ.get("B200COMM_REBUILD") == "1":
-        from . import build as _build
+def _build_module():
+    # import build.py WITHOUT going through the package (its import is in progress here)
+    import importlib.util
 
-        _build.build()
+    spec = importlib.util.spec_from_file_location("_b200comm_build", _PKG / "build.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _load() -> C.CDLL:
+    """Load the library; (re)build it first if it is missing or was built from different
+    sources (content digest, not mtimes: a snapshot copy must not trigger rebuilds)."""
+    mod = _build_module()
+    digest_file = LIB_PATH.with_name(LIB_PATH.name + ".digest")
+    want = mod.source_digest() if (mod.CSRC.is_dir() and os.environ.get("B200COMM_NO_AUTOBUILD") != "1") else None
+    have = digest_file.read_text().strip() if digest_file.exists() else None
+    if os.environ.get("B200COMM_REBUILD") == "1" or not LIB_PATH.exists() or (want and want != have):
+        import fcntl
+
+        LIB_PATH.parent.mkdir(parents=True, exist_ok=True)
+        with open(LIB_PATH.parent / ".build.lock", "w") as lock:     # one builder at a time
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            have = digest_file.read_text().strip() if digest_file.exists() else None
+            if os.environ.get("B200COMM_REBUILD") == "1" or not LIB_PATH.exists() or (want and want != have):
+                mod.build()
     return C.CDLL(str(LIB_PATH), mode=C.RTLD_GLOBAL)
 
 
@@ -86,7 +107,7 @@ class StencilInfo(C.Structure):
     _fields_ = [("cur", i32), ("steps_done", u64), ("grid", i32), ("threads", i32),
                 ("nstages", i32), ("tiles_x", i32), ("tiles_y", i32), ("ncoef", i32),
                 ("launches_per_step", i32), ("smem_bytes", sz), ("buf", vp * 2),
-                ("resid", vp)]
+                ("resid", vp), ("launches", u64)]
 
 
 # ---- core
@@ -119,6 +140,7 @@ _proto("b2c_stencil_set_timeout_ms", [vp, u64])
 _proto("b2c_stencil_info", [vp, C.POINTER(StencilInfo)])
 _proto("b2c_stencil_step", [vp, i32, i32, vp])
 _proto("b2c_stencil_drain", [vp, vp])
+_proto("b2c_stencil_advance", [vp, C.c_longlong])
 _proto("b2c_stencil_exchange_push", [vp, vp])
 _proto("b2c_stencil_exchange_wait", [vp, vp])
 _proto("b2c_stencil_fill", [vp, i32, i32, C.c_double, vp])

@@ -72,6 +72,18 @@ def _header_digest() -> str:
     return h.hexdigest()
 
 
+def source_digest() -> str:
+    """Hash of every native source and public header (+ the compile flags): identifies
+    what a built library was made from, independent of file times."""
+    h = hashlib.sha256(" ".join(NVCC_FLAGS + CXX_FLAGS).replace(str(REPO), "").encode())
+    files = [p for root in (CSRC, INCLUDE) for p in root.rglob("*")
+             if p.suffix in (".cu", ".cuh", ".cpp", ".hpp", ".h")]
+    for p in sorted(files):
+        h.update(str(p.relative_to(REPO)).encode())
+        h.update(p.read_bytes())
+    return h.hexdigest()
+
+
 def _obj_for(src: Path) -> Path:
     rel = src.relative_to(CSRC)
     return OBJ_DIR / ("_".join(rel.parts) + ".o")
@@ -121,6 +133,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         proc = subprocess.run(cmd, capture_output=True, text=True)
         if proc.returncode != 0:
             raise RuntimeError(f"link failed: {' '.join(cmd)}\n{proc.stdout}{proc.stderr}")
+    LIB_PATH.with_name(LIB_PATH.name + ".digest").write_text(source_digest())
     return LIB_PATH
 
 

@@ -79,7 +79,7 @@ class Stencil2D:
             if torch.cuda.is_available() else torch.empty(128, dtype=torch.float64)
         self._resid_pinned = torch.zeros(1, dtype=torch.float64).pin_memory() \
             if torch.cuda.is_available() else torch.zeros(1, dtype=torch.float64)
-        self.kernel_launches = 0
+        self._graph_launches = 0
 
     # ------------------------------------------------------------ factories
     @classmethod
@@ -124,6 +124,12 @@ class Stencil2D:
         return self.info().cur
 
     @property
+    def kernel_launches(self) -> int:
+        """Kernels launched through this plan so far, counted by the native library
+        (graph replays add the kernels of the captured batch)."""
+        return int(self.info().launches) + self._graph_launches
+
+    @property
     def padded(self) -> torch.Tensor:
         """Whole padded buffer holding the current state: ``rows x pitch``."""
         return self._buffer(self.current)
@@ -151,7 +157,6 @@ class Stencil2D:
                     _lib.check(_lib.lib.b2c_stencil_fill(self._h, b, 0, float(ghost_value), st))
                 if core_value is not None:
                     _lib.check(_lib.lib.b2c_stencil_fill(self._h, b, 1, float(core_value), st))
-        self.kernel_launches += 2 * ((ghost_value is not None) + (core_value is not None))
 
     def set_coeffs(self, coeffs: Sequence[float]) -> None:
         """Copy stencil coefficients host(pinned) -> device on the current stream."""
@@ -165,12 +170,10 @@ class Stencil2D:
     def exchange_push(self) -> None:
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_exchange_push(self._h, _stream_ptr(self.device)))
-        self.kernel_launches += 1
 
     def exchange_wait(self) -> None:
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_exchange_wait(self._h, _stream_ptr(self.device)))
-        self.kernel_launches += 1
 
     def exchange(self) -> None:
         """Unfused halo exchange of the current state (``ExchangeData``,
@@ -188,12 +191,32 @@ class Stencil2D:
         flags = (1 if residual else 0) | (2 if drain else 0)
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_step(self._h, nsteps, flags, _stream_ptr(self.device)))
-        self.kernel_launches += nsteps + (1 if residual and nsteps else 0) + (1 if drain else 0)
 
     def drain(self) -> None:
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_drain(self._h, _stream_ptr(self.device)))
-        self.kernel_launches += 1
+
+    def capture(self, nsteps: int, residual: bool = False, drain: bool = True) -> "StencilGraph":
+        """Capture ``nsteps`` fused steps (an EVEN number: the two buffers must be back in
+        place) into a CUDA graph.  Works because the epoch arithmetic of the kernels reads a
+        step counter in device memory, so the captured launch parameters stay valid for every
+        replay.  Run at least one plain :meth:`step` first (one-time kernel attributes are set
+        outside the capture)."""
+        if nsteps <= 0 or nsteps % 2:
+            raise ValueError("capture an even, positive number of steps")
+        g = torch.cuda.CUDAGraph()
+        launches0 = int(self.info().launches)
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                self.step(nsteps, residual=residual, drain=drain)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        per_replay = int(self.info().launches) - launches0
+        self._graph_launches -= per_replay      # captured, not executed
+        # nothing ran during capture: take the host-side bookkeeping back
+        _lib.check(_lib.lib.b2c_stencil_advance(self._h, -nsteps))
+        return StencilGraph(self, g, nsteps, per_replay)
 
     def local_residual_async(self) -> torch.Tensor:
         """Start the D2H copy of the last step's local sum of squared updates into
@@ -289,6 +312,18 @@ class Stencil2D:
             self.close()
         except Exception:
             pass
+
+
+class StencilGraph:
+    """A captured batch of fused steps (see :meth:`Stencil2D.capture`)."""
+
+    def __init__(self, stencil: "Stencil2D", graph, nsteps: int, launches: int):
+        self.stencil, self.graph, self.nsteps, self.launches = stencil, graph, nsteps, launches
+
+    def replay(self) -> None:
+        self.graph.replay()
+        _lib.check(_lib.lib.b2c_stencil_advance(self.stencil._h, self.nsteps))
+        self.stencil._graph_launches += self.launches
 
 
 class StencilGroup:

@@ -205,6 +205,7 @@ typedef struct {
     size_t smem_bytes;
     void* buf[2];
     double* resid;           /* device address of the last local residual */
+    unsigned long long launches; /* kernels launched through this plan so far */
 } b2c_stencil_info_t;
 
 /* Neighbour directions: 0 NW, 1 N, 2 NE, 3 W, 4 E, 5 SW, 6 S, 7 SE
@@ -218,6 +219,8 @@ int b2c_stencil_set_timeout_ms(b2c_stencil* s, unsigned long long ms);
 int b2c_stencil_info(b2c_stencil* s, b2c_stencil_info_t* out);
 /* flags: bit0 residual of the last step, bit1 drain the last step's halo */
 int b2c_stencil_step(b2c_stencil* s, int nsteps, int flags, void* stream);
+/* after replaying a captured CUDA graph of `nsteps` steps: advance the host-side step count */
+int b2c_stencil_advance(b2c_stencil* s, long long nsteps);
 int b2c_stencil_drain(b2c_stencil* s, void* stream);
 int b2c_stencil_exchange_push(b2c_stencil* s, void* stream);
 int b2c_stencil_exchange_wait(b2c_stencil* s, void* stream);

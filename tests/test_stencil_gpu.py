@@ -174,6 +174,34 @@ def test_checkpoint_resume_continues_bit_identically(tmp_path):
     assert torch.equal(grp2.gather_global(), want)
 
 
+@pytest.mark.parametrize("algo", ["tile", "strip"])
+def test_cuda_graph_replay_equals_plain_stepping(monkeypatch, algo):
+    """A captured batch of steps can be replayed because the kernels derive their epochs
+    from a device-side step counter; 2 plain + 3 x replay(4) must equal 14 plain steps."""
+    monkeypatch.setenv("B2C_STENCIL_ALGO", algo)
+    hw = (96, 512)
+    plain, glob = _run_group((1, 1), hw, 1, "star", 14)
+    want = plain.gather_global()
+    grp = Stencil2D.create_group(cms.LocalGroup(1), hw, 1, "star", dims=(1, 1))
+    s = grp.ranks[0]
+    s.fill(0.0, 0.0)
+    grp.scatter_global(glob)
+    grp.exchange()
+    s.step(2)                                    # also sets the one-time kernel attributes
+    torch.cuda.synchronize()
+    before = s.kernel_launches
+    graph = s.capture(4)
+    assert s.info().steps_done == 2 and s.kernel_launches == before
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    s.check()
+    assert s.info().steps_done == 14 and s.kernel_launches == before + 3 * graph.launches
+    assert torch.equal(grp.gather_global(), want)
+    with pytest.raises(ValueError):
+        s.capture(3)
+
+
 def test_exchange_reproduces_reference_golden_layout():
     """3x3 periodic grid, 16x16 tile, 5x5 stencil (ghost 2), core = rank id, ghosts = -1:
     after ONE device-side exchange every ghost block holds the id of the neighbour on
