@@ -193,7 +193,8 @@ def main(argv=None) -> int:
                             "D2H + host read, every step; wall clock, max over ranks",
                     "last_residual_sumsq": res},
             "gpu_launches": launches,
-            "launches_note": "per step: 1 fused stencil+halo kernel; +1 flag drain at the end",
+            "launches_note": "counted by the native plan: 1 fused stencil+halo kernel per step, then "
+                             "1 step-counter bump, 1 flag drain and 1 ghost-column unpack per batch",
         }
         print(json.dumps(out))
     world.barrier()
