@@ -102,6 +102,12 @@ class DistributedDot:
         self.launch(x, y, root)
         return self.result()
 
+    def set_timeout_ms(self, ms: int) -> None:
+        """Deadline of the device-side wait for the peers' partial sums."""
+        _L.b2c_dot_set_timeout_ms.argtypes = [C.c_void_p, C.c_ulonglong]
+        _L.b2c_dot_set_timeout_ms.restype = C.c_int
+        _lib.check(_L.b2c_dot_set_timeout_ms(self._h, int(ms)))
+
     def close(self) -> None:
         if self._h:
             _L.b2c_dot_destroy(self._h)
