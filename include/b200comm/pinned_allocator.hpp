@@ -5,13 +5,16 @@
 // construct/destroy specialisations :11-54, used by the async ping-pong under
 // -DPAGE_LOCKED, test-benchmark/mpi-pingpong-gpu-async.cpp:43-49).  This is the
 // C++17 form: allocator_traits supplies construct/destroy/rebind, so only
-// allocate/deallocate and equality are needed.  Header-only; needs the CUDA runtime.
+// allocate/deallocate and equality are needed.  Header-only; the page-locked
+// memory comes from the library (b2c_pinned_alloc), so a plain C++ program needs
+// neither the CUDA headers nor its own copy of the CUDA runtime.
 #pragma once
-#include <cuda_runtime.h>
-
 #include <cstddef>
 #include <limits>
 #include <new>
+#include <type_traits>
+
+#include "b200comm.h"
 
 namespace b200 {
 
@@ -27,13 +30,10 @@ public:
     T* allocate(std::size_t n) {
         if (n > std::numeric_limits<std::size_t>::max() / sizeof(T)) throw std::bad_array_new_length();
         void* p = nullptr;
-        if (cudaMallocHost(&p, n ? n * sizeof(T) : 1) != cudaSuccess || p == nullptr) {
-            cudaGetLastError();
-            throw std::bad_alloc();
-        }
+        if (b2c_pinned_alloc(&p, n * sizeof(T)) != 0 || p == nullptr) throw std::bad_alloc();
         return static_cast<T*>(p);
     }
-    void deallocate(T* p, std::size_t) noexcept { cudaFreeHost(p); }
+    void deallocate(T* p, std::size_t) noexcept { b2c_pinned_free(p); }
 };
 template <class T, class U>
 bool operator==(const PinnedAllocator<T>&, const PinnedAllocator<U>&) noexcept { return true; }
