@@ -36,6 +36,8 @@ def parse_args(argv=None):
     ap.add_argument("--tile", type=int, default=16384, help="cells per side of each GPU's tile")
     ap.add_argument("--radius", type=int, default=1)
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--temporal", type=int, default=1, choices=[1, 2],
+                    help="time steps per kernel sweep (2 = temporal blocking, radius 1 only)")
     ap.add_argument("--th", type=int, default=0, help="explicit per-GPU tile height (experiments)")
     ap.add_argument("--tw", type=int, default=0, help="explicit per-GPU tile width (experiments)")
     return ap.parse_args(argv)
@@ -79,7 +81,9 @@ def main(argv=None) -> int:
     if args.th and args.tw:
         th, tw = args.th, args.tw
     R = args.radius
-    st = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True)
+    T = args.temporal
+    args.steps += args.steps % T              # whole sweeps only; the JSON reports what was run
+    st = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True, temporal=T)
     dev = st.device
 
     # synthetic data: smooth deterministic field generated per tile on the device
@@ -104,7 +108,7 @@ def main(argv=None) -> int:
     sampler = ClockSampler(dev, period_ms=20).start() if world.rank == 0 else None
     if sampler is not None:
         sampler.wait_first(2.0)
-    st.step(max(args.warmup, 3))
+    st.step(-(-max(args.warmup, 3) // T) * T)
     torch.cuda.synchronize(dev)
     world.barrier()
     launches0 = st.kernel_launches
@@ -133,7 +137,7 @@ def main(argv=None) -> int:
     d2h = 8
     for _ in range(max(1, args.warmup)):
         st.set_coeffs(coef_host)
-        st.step(1, residual=True)
+        st.step(T, residual=True)
         st.local_residual_async()
         stream.synchronize()
     world.barrier()
@@ -142,9 +146,9 @@ def main(argv=None) -> int:
         sampler.window_begin()
     t0 = time.perf_counter()
     res = 0.0
-    for _ in range(args.steps):
+    for _ in range(args.steps // T):
         st.set_coeffs(coef_host)
-        st.step(1, residual=True)
+        st.step(T, residual=True)
         buf = st.local_residual_async()
         stream.synchronize()
         res = float(buf.item())
@@ -160,7 +164,7 @@ def main(argv=None) -> int:
     value = cells * args.steps / (ms_max * 1e-3) / 1e9
     e2e_value = cells * args.steps / e2e_s / 1e9
     if world.rank == 0:
-        bytes_per_cell = 16.0
+        bytes_per_cell = 16.0 / T   # one read + one write of the grid per sweep of T updates
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)),
@@ -182,15 +186,16 @@ def main(argv=None) -> int:
                        "parallelism": f"cart{dims[0]}x{dims[1]} 2-D domain decomposition",
                        "l2": "inputs larger than L2 (2 x %.2f GiB per GPU vs 126 MB)"
                              % (th * tw * 8 / 2 ** 30),
-                       "halo": "fused: peer stores + epoch flags inside the stencil kernel"},
+                       "halo": "fused: peer stores + epoch flags inside the stencil kernel",
+                       "time_steps_per_kernel_sweep": T},
             "roofline": {"hbm_gbs_measured": hbm,
                          "achieved_gbs_per_gpu": round(per_gpu * bytes_per_cell, 1),
                          "fraction_of_measured_hbm": round(per_gpu * bytes_per_cell / hbm, 4)},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 3), "unit": "Gcell/s",
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "what": "Stencil2D.set_coeffs(pinned) + step(1, residual=True) + residual "
-                            "D2H + host read, every step; wall clock, max over ranks",
+                    "h2d_bytes_per_step": h2d / T, "d2h_bytes_per_step": d2h / T,
+                    "what": f"Stencil2D.set_coeffs(pinned) + step({T}, residual=True) + residual "
+                            "D2H + host read, every kernel sweep; wall clock, max over ranks",
                     "last_residual_sumsq": res},
             "gpu_launches": launches,
             "launches_note": "counted by the native plan: 1 fused stencil+halo kernel per step, then "

@@ -155,10 +155,19 @@ __device__ __forceinline__ unsigned active_dirs(const LaunchParams& P, unsigned 
     return a;
 }
 
-template <int R, bool BOX, bool RESID, int NSTAGES>
-__global__ void __launch_bounds__(kThreads, (NSTAGES <= 3 && R <= 2) ? 2 : 1)
+// TB2 (temporal blocking, two time steps per sweep): the geometry, halo width and the
+// whole exchange protocol are those of R = 2 with corners, but the arithmetic is a
+// radius-1 star applied TWICE: each thread first forms the intermediate time level for its
+// two columns plus one column on either side from the shared-memory box (rows slide through
+// registers), then the second level from those registers.  One sweep reads and writes the
+// grid once for two updates, so the DRAM roofline is 8 bytes per cell update instead of 16.
+// Every value is computed with the same operation order as two single steps would use, on
+// this GPU or on the neighbour that owns the cell, so results stay bit-identical.
+template <int R, bool BOX, bool RESID, int NSTAGES, bool TB2 = false>
+__global__ void __launch_bounds__(kThreads, (NSTAGES <= 3 && R <= 2 && !TB2) ? 2 : 1)
 stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                      const __grid_constant__ LaunchParams P) {
+    static_assert(!TB2 || (R == 2 && !BOX), "temporal blocking: radius-1 star on the R = 2 geometry");
     using G = Geo<R>;
     extern __shared__ __align__(128) unsigned char smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + NSTAGES * G::STAGE_BYTES);
@@ -227,7 +236,7 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
     }
 
     // =============================== consumers ===============================
-    constexpr int NCOEF = BOX ? (2 * R + 1) * (2 * R + 1) : 4 * R + 1;
+    constexpr int NCOEF = TB2 ? 5 : (BOX ? (2 * R + 1) * (2 * R + 1) : 4 * R + 1);
     double c[NCOEF];
 #pragma unroll
     for (int k = 0; k < NCOEF; ++k) c[k] = __ldg(P.coef + k);
@@ -270,7 +279,63 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
         const double* mycol = box + c0 + G::RA;
 
         double2 res[kRowsPerThread];
-        if constexpr (!BOX) {
+        if constexpr (TB2) {
+            // in[]: three consecutive input rows, columns c0-2 .. c0+3 (three 16-byte loads
+            // per row); mid[]: three consecutive rows of the intermediate level, columns
+            // c0-1 .. c0+2.  Output row y needs intermediate rows y-1, y, y+1, which need input
+            // rows y-2 .. y+2: box rows r0 .. r0 + kRowsPerThread + 3.
+            double in[3][6], mid[3][4];
+            auto load_row = [&](double (&dst)[6], int box_row) {
+                const double* p = mycol + box_row * G::BOXW - 2;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const double2 v = *reinterpret_cast<const double2*>(p + 2 * k);
+                    dst[2 * k] = v.x;
+                    dst[2 * k + 1] = v.y;
+                }
+            };
+            load_row(in[0], r0);
+            load_row(in[1], r0 + 1);
+#pragma unroll
+            for (int j = 0; j < kRowsPerThread + 2; ++j) {
+                load_row(in[2], r0 + j + 2);
+                // intermediate row (tile row r0 - 1 + j) at columns c0-1 .. c0+2
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    double a = c[0] * in[1][k + 1];
+                    a = fma(c[1], in[1][k], a);          // west
+                    a = fma(c[2], in[1][k + 2], a);      // east
+                    a = fma(c[3], in[0][k + 1], a);      // north
+                    a = fma(c[4], in[2][k + 1], a);      // south
+                    mid[2][k] = a;
+                }
+                if (j >= 2) {
+                    const int y = j - 2;
+                    double ax = c[0] * mid[1][1], ay = c[0] * mid[1][2];
+                    ax = fma(c[1], mid[1][0], ax);
+                    ay = fma(c[1], mid[1][1], ay);
+                    ax = fma(c[2], mid[1][2], ax);
+                    ay = fma(c[2], mid[1][3], ay);
+                    ax = fma(c[3], mid[0][1], ax);
+                    ay = fma(c[3], mid[0][2], ay);
+                    ax = fma(c[4], mid[2][1], ax);
+                    ay = fma(c[4], mid[2][2], ay);
+                    res[y] = make_double2(ax, ay);
+                    if constexpr (RESID) {   // residual of the SECOND of the two updates
+                        const int gy = ty * kTileH + r0 + y, gx = tx * kTileW + c0;
+                        if (gy < P.H && gx < P.W) {
+                            const double dx_ = ax - mid[1][1], dy_ = ay - mid[1][2];
+                            racc = fma(dx_, dx_, racc);
+                            racc = fma(dy_, dy_, racc);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { in[0][k] = in[1][k]; in[1][k] = in[2][k]; }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { mid[0][k] = mid[1][k]; mid[1][k] = mid[2][k]; }
+            }
+        } else if constexpr (!BOX) {
             double2 win[2 * R + 1];
 #pragma unroll
             for (int k = 0; k < 2 * R; ++k)

@@ -190,7 +190,7 @@ static EncodeTiledFn get_encode_tiled() {
 
 struct Plan {
     Layout L;
-    int kind;          // 0 star, 1 box
+    int kind;          // 0 star, 1 box, 2 radius-1 star applied twice per sweep (L.R == 2)
     int push_corners;
     int device;
     unsigned char* base;         // my symmetric block
@@ -381,9 +381,9 @@ static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, c
     B200_CHECK_LAUNCH();
 }
 
-template <int R, bool BOX, bool RESID, int NST>
+template <int R, bool BOX, bool RESID, int NST, bool TB2 = false>
 static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) {
-    auto k = stencil_fused_kernel<R, BOX, RESID, NST>;
+    auto k = stencil_fused_kernel<R, BOX, RESID, NST, TB2>;
     static bool attr_done[64] = {};
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -406,7 +406,19 @@ static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStr
     else launch_one<R, BOX, false, NST>(pl, lp, st);
 }
 
+// kind 2: radius-1 star, two time steps per sweep, on the R = 2 geometry
+static void launch_tb2(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.nstages == 2) {
+        if (resid) launch_one<2, false, true, 2, true>(pl, lp, st);
+        else launch_one<2, false, false, 2, true>(pl, lp, st);
+        return;
+    }
+    if (resid) launch_one<2, false, true, 3, true>(pl, lp, st);
+    else launch_one<2, false, false, 3, true>(pl, lp, st);
+}
+
 static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.kind == 2) { launch_tb2(pl, lp, resid, st); return; }
     if (pl.algo == 1) {
         if (pl.L.R == 1) launch_strip<1>(pl, lp, resid, st);
         else launch_strip<2>(pl, lp, resid, st);
@@ -475,8 +487,9 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
                                   void* local_base, void* const nbr_base[8], int push_corners) {
     B2C_TRY
     B200_REQUIRE(out && local_base, ERR_ARG, "null argument");
-    B200_REQUIRE(kind == 0 || (kind == 1 && R <= 2), ERR_ARG,
-                 "kind must be 0 (star, R<=4) or 1 (box, R<=2)");
+    B200_REQUIRE(kind == 0 || (kind == 1 && R <= 2) || (kind == 2 && R == 2), ERR_ARG,
+                 "kind must be 0 (star, R<=4), 1 (box, R<=2) or 2 (radius-1 star x 2 time steps "
+                 "per sweep; pass R = 2, the ghost width)");
     b2c_stencil_layout_t tmp;
     int rc = b2c_stencil_layout(W, H, R, &tmp);
     if (rc) return rc;
@@ -486,7 +499,7 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
     std::memset(&p, 0, sizeof(p));
     p.L = make_layout(W, H, R);
     p.kind = kind;
-    p.push_corners = (kind == 1) ? 1 : (push_corners != 0);
+    p.push_corners = (kind != 0) ? 1 : (push_corners != 0);
     B200_CHECK_CUDA(cudaGetDevice(&p.device));
     p.base = static_cast<unsigned char*>(local_base);
     for (int d = 0; d < 8; ++d) p.nbr[d] = static_cast<unsigned char*>(nbr_base ? nbr_base[d] : nullptr);
@@ -509,11 +522,12 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         B200_CHECK_CUDA(cudaGetDeviceProperties(&pr, p.device));
         const long tiles_per_sm = (long)p.tilesX * p.tilesY / std::max(1, pr.multiProcessorCount);
         if (R <= 2 && tiles_per_sm >= 64) { p.nstages = 2; p.ctas_per_sm = 1; }
+        if (kind == 2) p.ctas_per_sm = 1;   // the two-level window needs the registers of a full SM
     }
     if (const char* te = std::getenv("B2C_TILE_STAGES"))
         if (R <= 2 && (std::atoi(te) == 2 || std::atoi(te) == 3)) p.nstages = std::atoi(te);
     if (const char* ce = std::getenv("B2C_TILE_CTAS_PER_SM"))
-        if (R <= 2 && (std::atoi(ce) == 1 || std::atoi(ce) == 2)) p.ctas_per_sm = std::atoi(ce);
+        if (R <= 2 && kind != 2 && (std::atoi(ce) == 1 || std::atoi(ce) == 2)) p.ctas_per_sm = std::atoi(ce);
     p.smem = p.nstages * stage + 2 * p.nstages * sizeof(uint64_t);
     cudaDeviceProp prop;
     B200_CHECK_CUDA(cudaGetDeviceProperties(&prop, p.device));
@@ -563,7 +577,7 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         bool use = false;
         if (ae && std::string(ae) == "strip") use = eligible;
         if (ae && std::string(ae) == "tile") use = false;
-        if (ae && std::string(ae) == "strip")
+        if (ae && std::string(ae) == "strip" && kind == 0)
             B200_REQUIRE(eligible, ERR_ARG, "strip kernel not applicable to this stencil/tile");
         p.algo = use ? 1 : 0;
     }
@@ -594,14 +608,14 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
                          "cuTensorMapEncodeTiled (strip) failed with CUresult " + std::to_string((int)r));
         }
     }
-    p.ncoef = kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1);
+    p.ncoef = kind == 2 ? 5 : (kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1));
     B200_CHECK_CUDA(cudaMalloc(&p.coef_dev, 128 * sizeof(double)));
     B200_CHECK_CUDA(cudaMalloc(&p.resid_partials,
                                (size_t)std::max(p.grid, p.strip_grid) * sizeof(double)));
     // default: Jacobi average of the 4R (or (2R+1)^2-1) neighbours
     double hc[128] = {0};
     const int nn = p.ncoef - 1;
-    if (kind == 0) { for (int k = 1; k < p.ncoef; ++k) hc[k] = 1.0 / nn; }
+    if (kind != 1) { for (int k = 1; k < p.ncoef; ++k) hc[k] = 1.0 / nn; }
     else { for (int k = 0; k < p.ncoef; ++k) hc[k] = (k == p.ncoef / 2) ? 0.0 : 1.0 / nn; }
     B200_CHECK_CUDA(cudaMemcpy(p.coef_dev, hc, sizeof(double) * p.ncoef, cudaMemcpyHostToDevice));
     *out = h;

@@ -47,6 +47,14 @@ def layout(W: int, H: int, radius: int) -> _lib.StencilLayout:
     return lay
 
 
+def _check_temporal(radius: int, kind: str, periods, temporal: int) -> None:
+    if temporal == 1:
+        return
+    if temporal != 2 or kind != "star" or radius != 1 or not all(bool(p) for p in periods):
+        raise ValueError("temporal blocking supports temporal=2 with a radius-1 star stencil on a "
+                         "fully periodic grid")
+
+
 def _stream_ptr(device: int) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
@@ -56,13 +64,15 @@ class Stencil2D:
     or :meth:`create_group` (virtual ranks in one process)."""
 
     def __init__(self, rank: int, cart: CartTopology, tile_hw: tuple[int, int], radius: int,
-                 kind: str, symbuf: SymmetricBuffer, push_corners: bool, world: World | None):
+                 kind: str, symbuf: SymmetricBuffer, push_corners: bool, world: World | None,
+                 temporal: int = 1):
         self.rank, self.cart, self.world = rank, cart, world
         self.H, self.W = int(tile_hw[0]), int(tile_hw[1])
-        self.radius, self.kind = radius, kind
+        self.radius, self.kind, self.temporal = radius, kind, int(temporal)
+        _check_temporal(radius, kind, cart.periods, self.temporal)
         self.symbuf = symbuf
         self.device = symbuf.device
-        self.layout = layout(self.W, self.H, radius)
+        self.layout = layout(self.W, self.H, radius * self.temporal)
         if symbuf.nbytes < self.layout.total_bytes:
             raise ValueError("symmetric block too small for this tile")
         self.neighbours = cart.neighbours8(rank)
@@ -71,7 +81,8 @@ class Stencil2D:
             nbr[d] = None if r == PROC_NULL else symbuf.peer_ptr(r)
         h = C.c_void_p()
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib.b2c_stencil_create(C.byref(h), self.W, self.H, radius, KIND[kind],
+            _lib.check(_lib.lib.b2c_stencil_create(C.byref(h), self.W, self.H, radius * self.temporal,
+                                                   2 if self.temporal == 2 else KIND[kind],
                                                    C.c_void_p(symbuf.local_ptr), C.byref(nbr),
                                                    int(push_corners)))
         self._h = h
@@ -85,27 +96,34 @@ class Stencil2D:
     @classmethod
     def create(cls, world: World, tile_hw: tuple[int, int], radius: int = 1, kind: str = "star",
                dims: Sequence[int] | None = None, periods=True,
-               push_corners: bool = True) -> "Stencil2D":
-        """Collective over ``world``: every rank gets an ``H x W`` tile."""
+               push_corners: bool = True, temporal: int = 1) -> "Stencil2D":
+        """Collective over ``world``: every rank gets an ``H x W`` tile.
+
+        ``temporal=2`` (radius-1 star on a fully periodic grid): temporal blocking -- every
+        sweep of the fused kernel advances TWO time steps from one read and one write of the
+        grid (ghost width 2, corners exchanged), bit-identical to two single steps.
+        :meth:`step` then takes an even number of steps."""
         dims = tuple(dims) if dims is not None else dims_create(world.size, 2)
         cart = CartTopology.create(dims, periods)
         if cart.size != world.size:
             raise ValueError(f"dims {dims} do not match world size {world.size}")
-        lay = layout(tile_hw[1], tile_hw[0], radius)
+        _check_temporal(radius, kind, cart.periods, temporal)
+        lay = layout(tile_hw[1], tile_hw[0], radius * temporal)
         sym = SymmetricBuffer.allocate(world, lay.total_bytes)
-        return cls(world.rank, cart, tile_hw, radius, kind, sym, push_corners, world)
+        return cls(world.rank, cart, tile_hw, radius, kind, sym, push_corners, world, temporal)
 
     @classmethod
     def create_group(cls, group: LocalGroup, tile_hw: tuple[int, int], radius: int = 1,
                      kind: str = "star", dims: Sequence[int] | None = None, periods=True,
-                     push_corners: bool = True) -> "StencilGroup":
+                     push_corners: bool = True, temporal: int = 1) -> "StencilGroup":
         dims = tuple(dims) if dims is not None else dims_create(group.size, 2)
         cart = CartTopology.create(dims, periods)
         if cart.size != group.size:
             raise ValueError(f"dims {dims} do not match group size {group.size}")
-        lay = layout(tile_hw[1], tile_hw[0], radius)
+        _check_temporal(radius, kind, cart.periods, temporal)
+        lay = layout(tile_hw[1], tile_hw[0], radius * temporal)
         syms = SymmetricBuffer.allocate_local(group, lay.total_bytes)
-        return StencilGroup([cls(r, cart, tile_hw, radius, kind, syms[r], push_corners, None)
+        return StencilGroup([cls(r, cart, tile_hw, radius, kind, syms[r], push_corners, None, temporal)
                              for r in range(group.size)])
 
     # ------------------------------------------------------------ views
@@ -187,10 +205,22 @@ class Stencil2D:
 
     # ------------------------------------------------------------ stepping
     def step(self, nsteps: int = 1, residual: bool = False, drain: bool = True) -> None:
-        """Enqueue ``nsteps`` fused update+halo steps on the current stream."""
+        """Enqueue ``nsteps`` fused update+halo steps on the current stream (a multiple of
+        ``temporal``: with temporal blocking one kernel advances two time steps)."""
         flags = (1 if residual else 0) | (2 if drain else 0)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib.b2c_stencil_step(self._h, nsteps, flags, _stream_ptr(self.device)))
+            _lib.check(_lib.lib.b2c_stencil_step(self._h, self._sweeps(nsteps), flags,
+                                                 _stream_ptr(self.device)))
+
+    def _sweeps(self, nsteps: int) -> int:
+        if nsteps % self.temporal:
+            raise ValueError(f"with temporal={self.temporal} the step count must be a multiple of it")
+        return nsteps // self.temporal
+
+    @property
+    def steps_done(self) -> int:
+        """Time steps completed since creation."""
+        return int(self.info().steps_done) * self.temporal
 
     def drain(self) -> None:
         with torch.cuda.device(self.device):
@@ -202,8 +232,9 @@ class Stencil2D:
         step counter in device memory, so the captured launch parameters stay valid for every
         replay.  Run at least one plain :meth:`step` first (one-time kernel attributes are set
         outside the capture)."""
-        if nsteps <= 0 or nsteps % 2:
-            raise ValueError("capture an even, positive number of steps")
+        if nsteps <= 0 or nsteps % (2 * self.temporal):
+            raise ValueError("capture a positive number of steps that is a multiple of "
+                             f"{2 * self.temporal} (an even number of kernel sweeps)")
         g = torch.cuda.CUDAGraph()
         launches0 = int(self.info().launches)
         side = torch.cuda.Stream(self.device)
@@ -215,7 +246,7 @@ class Stencil2D:
         per_replay = int(self.info().launches) - launches0
         self._graph_launches -= per_replay      # captured, not executed
         # nothing ran during capture: take the host-side bookkeeping back
-        _lib.check(_lib.lib.b2c_stencil_advance(self._h, -nsteps))
+        _lib.check(_lib.lib.b2c_stencil_advance(self._h, -self._sweeps(nsteps)))
         return StencilGraph(self, g, nsteps, per_replay)
 
     def local_residual_async(self) -> torch.Tensor:
@@ -253,6 +284,7 @@ class Stencil2D:
         done, res = 0, None
         while done < max_steps:
             n = min(check_every, max_steps - done)
+            n = max(self.temporal, n - n % self.temporal)
             self.step(n, residual=True)
             done += n
             res = self.residual()
@@ -287,7 +319,7 @@ class Stencil2D:
         The reference has no checkpointing, only the per-rank text dump
         (``mpi-2d-stencil-subarray-cuda.cu:114-119,164-176``); this is the binary form of it."""
         torch.cuda.current_stream(self.device).synchronize()
-        torch.save({"tile": self.tile.cpu(), "steps_done": int(self.info().steps_done),
+        torch.save({"tile": self.tile.cpu(), "steps_done": self.steps_done, "temporal": self.temporal,
                     "rank": self.rank, "dims": self.cart.dims, "periods": self.cart.periods,
                     "tile_hw": (self.H, self.W), "radius": self.radius, "kind": self.kind}, path)
 
@@ -296,7 +328,8 @@ class Stencil2D:
         ghost cells) and return the step count of the checkpoint.  Call :meth:`exchange`
         afterwards (collective) before stepping again."""
         ck = torch.load(path)
-        if tuple(ck["tile_hw"]) != (self.H, self.W) or ck["radius"] != self.radius or ck["rank"] != self.rank:
+        if tuple(ck["tile_hw"]) != (self.H, self.W) or ck["radius"] != self.radius \
+                or ck["rank"] != self.rank or ck.get("temporal", 1) != self.temporal:
             raise ValueError("checkpoint does not match this plan (tile size, radius or rank)")
         self.tile.copy_(ck["tile"].to(self.tile.device))
         torch.cuda.current_stream(self.device).synchronize()
@@ -322,7 +355,7 @@ class StencilGraph:
 
     def replay(self) -> None:
         self.graph.replay()
-        _lib.check(_lib.lib.b2c_stencil_advance(self.stencil._h, self.nsteps))
+        _lib.check(_lib.lib.b2c_stencil_advance(self.stencil._h, self.stencil._sweeps(self.nsteps)))
         self.stencil._graph_launches += self.launches
 
 
@@ -359,10 +392,12 @@ class StencilGroup:
 
     def step(self, nsteps: int = 1, residual: bool = False) -> None:
         multi_dev = len({s.device for s in self.ranks}) > 1
-        for i in range(nsteps):
-            last = i == nsteps - 1
+        t = self.ranks[0].temporal
+        nsweeps = self.ranks[0]._sweeps(nsteps)
+        for i in range(nsweeps):
+            last = i == nsweeps - 1
             for s in self.ranks:
-                s.step(1, residual=residual and last, drain=False)
+                s.step(t, residual=residual and last, drain=False)
             if multi_dev:
                 # different devices run concurrently: keep ranks within one step
                 # of each other exactly like separate processes would be

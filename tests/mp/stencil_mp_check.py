@@ -19,9 +19,10 @@ def main():
     world = cms.init()
     dims = cms.dims_create(world.size)
     fails = 0
-    for (th, tw, R, kind, steps) in [(64, 256, 1, "star", 7), (96, 384, 2, "star", 5),
-                                      (50, 200, 1, "box", 4), (1024, 2048, 1, "star", 20)]:
-        st = Stencil2D.create(world, (th, tw), R, kind, dims=dims)
+    for (th, tw, R, kind, steps, tb) in [(64, 256, 1, "star", 7, 1), (96, 384, 2, "star", 5, 1),
+                                          (50, 200, 1, "box", 4, 1), (1024, 2048, 1, "star", 20, 1),
+                                          (64, 256, 1, "star", 8, 2), (1024, 2048, 1, "star", 20, 2)]:
+        st = Stencil2D.create(world, (th, tw), R, kind, dims=dims, temporal=tb)
         g = torch.Generator().manual_seed(1234)
         glob = torch.rand(dims[0] * th, dims[1] * tw, dtype=torch.float64, generator=g)
         r, c = st.cart.coords(world.rank)
@@ -43,15 +44,16 @@ def main():
         ok = err < 1e-12 and abs(res - want_res) <= 1e-10 * want_res
         # ghosts of the current buffer must hold the neighbours' cores after the drain
         tile = st.tile.cpu()
-        ri = (torch.arange(-R, th + R) + r * th) % exp.shape[0]
-        ci = (torch.arange(-R, tw + R) + c * tw) % exp.shape[1]
+        gw = R * tb
+        ri = (torch.arange(-gw, th + gw) + r * th) % exp.shape[0]
+        ci = (torch.arange(-gw, tw + gw) + c * tw) % exp.shape[1]
         gp = exp[ri][:, ci]
         if kind == "star":  # corners are exchanged too (push_corners=True by default)
             pass
         gerr = float((tile - gp).abs().max())
         ok = ok and gerr < 1e-12
         fails += 0 if ok else 1
-        print(f"rank {world.rank} dims {dims} tile {th}x{tw} R{R} {kind}: err {err:.2e} "
+        print(f"rank {world.rank} dims {dims} tile {th}x{tw} R{R} {kind} temporal {tb}: err {err:.2e} "
               f"ghost err {gerr:.2e} resid {res:.6e} (want {want_res:.6e}) {'OK' if ok else 'FAIL'}",
               flush=True)
         world.barrier()

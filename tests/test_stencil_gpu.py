@@ -23,9 +23,10 @@ def _rand_global(h, w, seed=0):
     return torch.rand(h, w, dtype=torch.float64, generator=g)
 
 
-def _run_group(dims, tile_hw, radius, kind, steps, coeffs=None, periods=True, seed=0):
+def _run_group(dims, tile_hw, radius, kind, steps, coeffs=None, periods=True, seed=0, temporal=1):
     n = dims[0] * dims[1]
-    grp = Stencil2D.create_group(cms.LocalGroup(n), tile_hw, radius, kind, dims=dims, periods=periods)
+    grp = Stencil2D.create_group(cms.LocalGroup(n), tile_hw, radius, kind, dims=dims, periods=periods,
+                                 temporal=temporal)
     glob = _rand_global(dims[0] * tile_hw[0], dims[1] * tile_hw[1], seed)
     for s in grp.ranks:
         s.fill(0.0, 0.0)
@@ -136,6 +137,61 @@ def test_both_kernels_agree_bitwise_and_match_oracle(monkeypatch, algo, dims, ti
     ri = (torch.arange(-R, tile_hw[0] + R)) % exp.shape[0]
     ci = (torch.arange(-R, tile_hw[1] + R)) % exp.shape[1]
     assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
+
+
+@pytest.mark.parametrize("dims,tile_hw", [((1, 1), (96, 384)), ((2, 2), (64, 256)), ((2, 4), (40, 504)),
+                                          ((3, 3), (32, 260)), ((1, 2), (50, 200)), ((1, 1), (256, 1024))])
+def test_temporal_blocking_is_bit_identical_to_single_steps(dims, tile_hw):
+    """temporal=2: one sweep = two time steps (ghost width 2, corners exchanged).  Same bits as
+    the single-step kernel, same residual (of the last update), complete ghost ring."""
+    steps = 6
+    coeffs = [0.1, 0.2, 0.25, 0.15, 0.3]
+    tb, glob = _run_group(dims, tile_hw, 1, "star", steps, coeffs, temporal=2)
+    one, _ = _run_group(dims, tile_hw, 1, "star", steps, coeffs)
+    got = tb.gather_global()
+    assert torch.equal(got, one.gather_global())
+    exp = glob.clone()
+    for _ in range(steps):
+        exp = reference_step(exp, coeffs, 1)
+    assert torch.allclose(got, exp, rtol=1e-12, atol=1e-13)
+    assert tb.residual() == pytest.approx(one.residual(), rel=1e-12)
+    s = tb.ranks[0]
+    assert s.steps_done == steps and s.layout.ghost == 2
+    ri = (torch.arange(-2, tile_hw[0] + 2)) % exp.shape[0]
+    ci = (torch.arange(-2, tile_hw[1] + 2)) % exp.shape[1]
+    assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
+    with pytest.raises(ValueError):
+        s.step(3)
+
+
+def test_temporal_blocking_rejects_what_it_cannot_do():
+    with pytest.raises(ValueError):
+        Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 2, "star", dims=(1, 1), temporal=2)
+    with pytest.raises(ValueError):
+        Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 1, "star", dims=(1, 1), periods=False, temporal=2)
+    with pytest.raises(ValueError):
+        Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 1, "box", dims=(1, 1), temporal=2)
+
+
+def test_temporal_blocking_graph_replay():
+    hw = (96, 512)
+    plain, glob = _run_group((1, 1), hw, 1, "star", 14)
+    grp = Stencil2D.create_group(cms.LocalGroup(1), hw, 1, "star", dims=(1, 1), temporal=2)
+    s = grp.ranks[0]
+    s.fill(0.0, 0.0)
+    grp.scatter_global(glob)
+    grp.exchange()
+    s.step(2)
+    torch.cuda.synchronize()
+    graph = s.capture(4)
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    s.check()
+    assert s.steps_done == 14
+    assert torch.equal(grp.gather_global(), plain.gather_global())
+    with pytest.raises(ValueError):
+        s.capture(2)
 
 
 def test_missing_neighbour_times_out_instead_of_hanging():
