@@ -5,7 +5,10 @@ Metric (BASELINE.json): 2D-stencil Gcell-updates/s at 1/2/4/8 B200, device
 timed, max over ranks.  Weak scaling: every GPU owns a 16384^2 tile of a
 periodic Py x Px Cartesian grid (1x1, 1x2, 2x2, 2x4); one step = one Jacobi
 sweep of every tile INCLUDING the halo exchange, which is fused into the same
-kernel (peer stores over NVLink + device-side epoch flags).
+kernel (peer stores over NVLink + device-side epoch flags).  By default the kernel is the
+temporally blocked one (``--temporal 2``): every sweep over the grid advances TWO time steps
+(ghost width 2, corners exchanged), bit-identical to two single steps, so the grid is read
+and written once per two updates; the JSON also carries the ``--temporal 1`` number.
 
     python bench.py --gpus 1 --steps 20 --warmup 3
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
@@ -36,8 +39,9 @@ def parse_args(argv=None):
     ap.add_argument("--tile", type=int, default=16384, help="cells per side of each GPU's tile")
     ap.add_argument("--radius", type=int, default=1)
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--temporal", type=int, default=1, choices=[1, 2],
-                    help="time steps per kernel sweep (2 = temporal blocking, radius 1 only)")
+    ap.add_argument("--temporal", type=int, default=0, choices=[0, 1, 2],
+                    help="time steps per kernel sweep: 2 = temporal blocking (radius 1 only), "
+                         "1 = one step per sweep, 0 = 2 where possible")
     ap.add_argument("--th", type=int, default=0, help="explicit per-GPU tile height (experiments)")
     ap.add_argument("--tw", type=int, default=0, help="explicit per-GPU tile width (experiments)")
     return ap.parse_args(argv)
@@ -81,25 +85,29 @@ def main(argv=None) -> int:
     if args.th and args.tw:
         th, tw = args.th, args.tw
     R = args.radius
-    T = args.temporal
+    T = args.temporal or (2 if R == 1 else 1)
     args.steps += args.steps % T              # whole sweeps only; the JSON reports what was run
-    st = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True, temporal=T)
-    dev = st.device
-
-    # synthetic data: smooth deterministic field generated per tile on the device
-    # (state, like weights: it stays resident; per-step INPUTS are the coefficients)
-    r, c = st.cart.coords(world.rank)
-    ys = torch.arange(th, device=f"cuda:{dev}", dtype=torch.float64) + r * th
-    xs = torch.arange(tw, device=f"cuda:{dev}", dtype=torch.float64) + c * tw
-    st.fill(0.0, 0.0)
-    st.core.copy_(torch.sin(ys * 1e-3)[:, None] * torch.cos(xs * 2e-3)[None, :])
-    del ys, xs
     coeffs = jacobi_coeffs(R)
-    st.set_coeffs(coeffs)
-    torch.cuda.synchronize(dev)
-    st.exchange()
-    torch.cuda.synchronize(dev)
-    world.barrier()
+
+    def make_plan(temporal):
+        # synthetic data: smooth deterministic field generated per tile on the device
+        # (state, like weights: it stays resident; per-step INPUTS are the coefficients)
+        p = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True,
+                             temporal=temporal)
+        r, c = p.cart.coords(world.rank)
+        ys = torch.arange(th, device=f"cuda:{p.device}", dtype=torch.float64) + r * th
+        xs = torch.arange(tw, device=f"cuda:{p.device}", dtype=torch.float64) + c * tw
+        p.fill(0.0, 0.0)
+        p.core.copy_(torch.sin(ys * 1e-3)[:, None] * torch.cos(xs * 2e-3)[None, :])
+        p.set_coeffs(coeffs)
+        torch.cuda.synchronize(p.device)
+        p.exchange()
+        torch.cuda.synchronize(p.device)
+        world.barrier()
+        return p
+
+    st = make_plan(T)
+    dev = st.device
 
     stream = torch.cuda.current_stream(dev)
     # ---------------- device-timed: K fused steps ----------------
@@ -160,6 +168,23 @@ def main(argv=None) -> int:
     clocks = sampler.stop() if sampler is not None else None
     st.check()
 
+    # transparency: the same K steps with ONE time step per kernel sweep (no temporal blocking)
+    single = None
+    if T > 1:
+        st.close()
+        st1 = make_plan(1)
+        st1.step(max(args.warmup, 3))
+        torch.cuda.synchronize(dev)
+        world.barrier()
+        e0.record(stream)
+        st1.step(args.steps)
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        ms1 = world.allreduce_max(e0.elapsed_time(e1))
+        st1.check()
+        single = ms1
+        st1.close()
+
     cells = float(th) * float(tw) * n
     value = cells * args.steps / (ms_max * 1e-3) / 1e9
     e2e_value = cells * args.steps / e2e_s / 1e9
@@ -180,7 +205,9 @@ def main(argv=None) -> int:
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "fp64", "data": "synthetic",
             "impl": "ours",
-            "config": {"model": f"stencil2d star radius {R} ({4 * R + 1}-point) Jacobi, periodic",
+            "config": {"model": f"stencil2d star radius {R} ({4 * R + 1}-point) Jacobi, periodic"
+                                + (f", {T} time steps per kernel sweep (temporal blocking, bit-identical "
+                                   "to single steps)" if T > 1 else ""),
                        "tile_per_gpu": [th, tw], "global_grid": [th * dims[0], tw * dims[1]],
                        "process_grid": list(dims), "global_batch": int(cells), "seq_len": None,
                        "parallelism": f"cart{dims[0]}x{dims[1]} 2-D domain decomposition",
@@ -197,13 +224,19 @@ def main(argv=None) -> int:
                     "what": f"Stencil2D.set_coeffs(pinned) + step({T}, residual=True) + residual "
                             "D2H + host read, every kernel sweep; wall clock, max over ranks",
                     "last_residual_sumsq": res},
+            "one_time_step_per_sweep": None if single is None else {
+                "value": round(cells * args.steps / (single * 1e-3) / 1e9, 3), "unit": "Gcell/s",
+                "ms_per_step": round(single / args.steps, 5),
+                "what": "same grid and K steps without temporal blocking (--temporal 1), device timed"},
             "gpu_launches": launches,
-            "launches_note": "counted by the native plan: 1 fused stencil+halo kernel per step, then "
-                             "1 step-counter bump, 1 flag drain and 1 ghost-column unpack per batch",
+            "launches_note": "counted by the native plan: 1 fused stencil+halo kernel per sweep "
+                             f"({T} time step(s) each), then 1 step-counter bump, 1 flag drain and "
+                             "1 ghost-column unpack per batch",
         }
         print(json.dumps(out))
     world.barrier()
-    st.close()
+    if single is None:
+        st.close()
     world.finalize()
     return 0
 

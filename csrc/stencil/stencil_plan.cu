@@ -408,13 +408,23 @@ static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStr
 
 // kind 2: radius-1 star, two time steps per sweep, on the R = 2 geometry
 static void launch_tb2(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
-    if (pl.nstages == 2) {
-        if (resid) launch_one<2, false, true, 2, true>(pl, lp, st);
-        else launch_one<2, false, false, 2, true>(pl, lp, st);
-        return;
+    switch (pl.nstages) {
+        case 2:
+            if (resid) launch_one<2, false, true, 2, true>(pl, lp, st);
+            else launch_one<2, false, false, 2, true>(pl, lp, st);
+            return;
+        case 4:
+            if (resid) launch_one<2, false, true, 4, true>(pl, lp, st);
+            else launch_one<2, false, false, 4, true>(pl, lp, st);
+            return;
+        case 5:
+            if (resid) launch_one<2, false, true, 5, true>(pl, lp, st);
+            else launch_one<2, false, false, 5, true>(pl, lp, st);
+            return;
+        default:
+            if (resid) launch_one<2, false, true, 3, true>(pl, lp, st);
+            else launch_one<2, false, false, 3, true>(pl, lp, st);
     }
-    if (resid) launch_one<2, false, true, 3, true>(pl, lp, st);
-    else launch_one<2, false, false, 3, true>(pl, lp, st);
 }
 
 static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
@@ -522,10 +532,15 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         B200_CHECK_CUDA(cudaGetDeviceProperties(&pr, p.device));
         const long tiles_per_sm = (long)p.tilesX * p.tilesY / std::max(1, pr.multiProcessorCount);
         if (R <= 2 && tiles_per_sm >= 64) { p.nstages = 2; p.ctas_per_sm = 1; }
-        if (kind == 2) p.ctas_per_sm = 1;   // the two-level window needs the registers of a full SM
+        // Two time steps per sweep: one CTA per SM (the two-level register window is wide) and
+        // a 3-stage ring -- the compute phase per tile is ~2x longer than a single step's, so
+        // more has to be in flight to cover it (measured 16384^2: 2/3 stages = 696/783 Gcell/s).
+        if (kind == 2) { p.ctas_per_sm = 1; p.nstages = 3; }
     }
-    if (const char* te = std::getenv("B2C_TILE_STAGES"))
-        if (R <= 2 && (std::atoi(te) == 2 || std::atoi(te) == 3)) p.nstages = std::atoi(te);
+    if (const char* te = std::getenv("B2C_TILE_STAGES")) {
+        const int v = std::atoi(te);
+        if (R <= 2 && (v == 2 || v == 3 || (kind == 2 && (v == 4 || v == 5)))) p.nstages = v;
+    }
     if (const char* ce = std::getenv("B2C_TILE_CTAS_PER_SM"))
         if (R <= 2 && kind != 2 && (std::atoi(ce) == 1 || std::atoi(ce) == 2)) p.ctas_per_sm = std::atoi(ce);
     p.smem = p.nstages * stage + 2 * p.nstages * sizeof(uint64_t);

@@ -8,9 +8,12 @@ racy ``NO_SYNC`` variant (``:26-32``), print GPU vs CPU.
 Also shown: the framework's own kernel on one rank, and the entry point that allocates nothing.
 """
 import ctypes as C
+import os
 import sys
 
 import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 
 import cuda_mpi_scratch_b200 as cms
 from cuda_mpi_scratch_b200 import _lib
