@@ -90,6 +90,62 @@ template <typename T> __device__ __forceinline__ T apply(T a, T b, int op) {
     }
 }
 
+// 16-byte lanes: all bulk work of the reductions is done on int4 vectors of the STAGING
+// buffers (256-byte aligned, padded past n), four independent vectors per thread in flight.
+template <typename T> __device__ __forceinline__ int4 apply_vec(int4 a, const int4 b, int op) {
+    constexpr int N = 16 / (int)sizeof(T);
+    T* pa = reinterpret_cast<T*>(&a);
+    const T* pb = reinterpret_cast<const T*>(&b);
+#pragma unroll
+    for (int k = 0; k < N; ++k) pa[k] = apply(pa[k], pb[k], op);
+    return a;
+}
+constexpr int kVecUnroll = 4;
+
+// acc[k] = op over ranks (fixed rank order: same bits on every rank) of vector v0 + k*stride
+template <typename T>
+__device__ __forceinline__ void reduce_vecs(const Ws& w, uint64_t epoch, int64_t v0, int64_t stride,
+                                            int64_t vend, int op, int4 (&acc)[kVecUnroll]) {
+    const int4* base0 = reinterpret_cast<const int4*>(in_half(w, 0, epoch));
+#pragma unroll
+    for (int k = 0; k < kVecUnroll; ++k)
+        if (v0 + k * stride < vend) acc[k] = __ldcv(base0 + v0 + k * stride);
+    for (int r = 1; r < w.nranks; ++r) {
+        const int4* base = reinterpret_cast<const int4*>(in_half(w, r, epoch));
+        int4 t[kVecUnroll];
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v0 + k * stride < vend) t[k] = __ldcv(base + v0 + k * stride);
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v0 + k * stride < vend) acc[k] = apply_vec<T>(acc[k], t[k], op);
+    }
+}
+
+// Copy n elements from (16-byte aligned) staging to a user pointer of any alignment.
+template <typename T>
+__device__ __forceinline__ void copy_out(T* out, const T* src, int64_t n) {
+    constexpr int E = 16 / (int)sizeof(T);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+        const int64_t nv = n / E;
+        const int4* s4 = reinterpret_cast<const int4*>(src);
+        int4* d4 = reinterpret_cast<int4*>(out);
+        for (int64_t v = tid; v < nv; v += nthr * kVecUnroll) {
+            int4 t[kVecUnroll];
+#pragma unroll
+            for (int k = 0; k < kVecUnroll; ++k)
+                if (v + k * nthr < nv) t[k] = __ldcv(s4 + v + k * nthr);
+#pragma unroll
+            for (int k = 0; k < kVecUnroll; ++k)
+                if (v + k * nthr < nv) d4[v + k * nthr] = t[k];
+        }
+        for (int64_t i = nv * E + tid; i < n; i += nthr) out[i] = *reinterpret_cast<const volatile T*>(src + i);
+    } else {
+        for (int64_t i = tid; i < n; i += nthr) out[i] = *reinterpret_cast<const volatile T*>(src + i);
+    }
+}
+
 // ---- one-shot allreduce / reduce ------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __grid_constant__ Ws w, T* out,
@@ -102,10 +158,20 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __gri
     if (!(phases & 2)) return;
     if (root >= 0 && w.rank != root) return;
     wait_all(w, kOffReady, epoch);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-         i += (int64_t)gridDim.x * blockDim.x) {
+    constexpr int E = 16 / (int)sizeof(T);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    const bool aligned = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    const int64_t nv = aligned ? n / E : 0;
+    for (int64_t v = tid; v < nv; v += nthr * kVecUnroll) {
+        int4 acc[kVecUnroll];
+        reduce_vecs<T>(w, epoch, v, nthr, nv, op, acc);
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v + k * nthr < nv) reinterpret_cast<int4*>(out)[v + k * nthr] = acc[k];
+    }
+    for (int64_t i = nv * E + tid; i < n; i += nthr) {     // tail, or everything if `out` is unaligned
         T acc = *reinterpret_cast<const volatile T*>(reinterpret_cast<const T*>(in_half(w, 0, epoch)) + i);
-        for (int r = 1; r < w.nranks; ++r)   // fixed rank order: same bits on every rank
+        for (int r = 1; r < w.nranks; ++r)
             acc = apply(acc, *reinterpret_cast<const volatile T*>(
                                  reinterpret_cast<const T*>(in_half(w, r, epoch)) + i), op);
         out[i] = acc;
@@ -113,26 +179,32 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __gri
 }
 
 // ---- two-shot allreduce: reduce-scatter into everybody's OUT, then copy out -----
+// Works on whole 16-byte vectors of the padded staging buffers; rank r owns vectors
+// [r*vchunk, (r+1)*vchunk).
 template <typename T>
 __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(const __grid_constant__ Ws w, T* out,
                                                                      int64_t n, int op, uint64_t epoch,
                                                                      int phases) {
     const int P = w.nranks;
-    const int64_t chunk = (n + P - 1) / P;
-    const int64_t lo = (int64_t)w.rank * chunk, hi = min(n, lo + chunk);
+    const int64_t nvec = (n * (int64_t)sizeof(T) + 15) / 16;
+    const int64_t vchunk = (nvec + P - 1) / P;
+    const int64_t lo = min(nvec, (int64_t)w.rank * vchunk), hi = min(nvec, lo + vchunk);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
     __shared__ bool last;
     if (phases & 1) {
         if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
     }
     if (phases & 2) {
         wait_all(w, kOffReady, epoch);
-        for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
-             i += (int64_t)gridDim.x * blockDim.x) {
-            T acc = *reinterpret_cast<const volatile T*>(reinterpret_cast<const T*>(in_half(w, 0, epoch)) + i);
-            for (int r = 1; r < P; ++r)
-                acc = apply(acc, *reinterpret_cast<const volatile T*>(
-                                     reinterpret_cast<const T*>(in_half(w, r, epoch)) + i), op);
-            for (int r = 0; r < P; ++r) reinterpret_cast<T*>(out_half(w, r, epoch))[i] = acc;
+        for (int64_t v = lo + tid; v < hi; v += nthr * kVecUnroll) {
+            int4 acc[kVecUnroll];
+            reduce_vecs<T>(w, epoch, v, nthr, hi, op, acc);
+            for (int r = 0; r < P; ++r) {
+                int4* dst = reinterpret_cast<int4*>(out_half(w, r, epoch));
+#pragma unroll
+                for (int k = 0; k < kVecUnroll; ++k)
+                    if (v + k * nthr < hi) dst[v + k * nthr] = acc[k];
+            }
         }
         // my chunk is complete when the LAST CTA has stored it
         __syncthreads();
@@ -146,10 +218,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(const __gri
     }
     if (phases & 4) {
         wait_all(w, kOffDone, epoch);
-        const T* src = reinterpret_cast<const T*>(out_half(w, w.rank, epoch));
-        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-             i += (int64_t)gridDim.x * blockDim.x)
-            out[i] = *reinterpret_cast<const volatile T*>(src + i);
+        copy_out<T>(out, reinterpret_cast<const T*>(out_half(w, w.rank, epoch)), n);
     }
 }
 
@@ -233,7 +302,8 @@ static void launch_allreduce(Plan& p, void* out, int64_t n, int op, int root, in
     // two-shot CTAs wait (phase 4) for a flag that needs EVERY CTA of this grid to have
     // finished phase 2: the grid must be co-resident, so stay well below capacity
     const int per_sm = (algo == 1 && root < 0) ? 2 : 4;
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + kThreads - 1) / kThreads, p.sms * per_sm));
+    const int64_t nvec = (n * (int64_t)sizeof(T) + 15) / 16;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + kThreads - 1) / kThreads, p.sms * per_sm));
     if (algo == 1 && root < 0)
         allreduce_twoshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, p.epoch, phases);
     else

@@ -29,6 +29,23 @@ def test_allreduce_sum_matches_torch_and_is_identical_everywhere(algo, P, n, dty
         assert torch.allclose(ts[0].double(), want, rtol=tol, atol=tol)
 
 
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot"])
+def test_allreduce_unaligned_tensors_and_odd_lengths(algo):
+    """The kernels work on 16-byte vectors of the staging buffers; user tensors that start at
+    an odd element (not 16-byte aligned) and odd lengths take the scalar copy-out path."""
+    P = 3
+    grp = DeviceCollectives.create_group(cms.LocalGroup(P), max_bytes=1 << 20)
+    for n in (1, 3, 1023, 4099):
+        bases = [torch.arange(n + 1, dtype=torch.float32, device="cuda") * (r + 1) for r in range(P)]
+        ts = [b[1:] for b in bases]                  # data_ptr() % 16 == 4
+        want = sum((r + 1) for r in range(P)) * torch.arange(1, n + 1, dtype=torch.float32, device="cuda")
+        grp.allreduce(ts, "sum", algo)
+        grp.check()
+        for r in range(P):
+            assert torch.equal(ts[r], want)
+            assert float(bases[r][0]) == 0.0         # the element before the view is untouched
+
+
 def test_allreduce_max_min_and_reduce_to_root():
     P, n = 4, 5000
     grp = DeviceCollectives.create_group(cms.LocalGroup(P), max_bytes=1 << 20)
