@@ -6,9 +6,9 @@ timed, max over ranks.  Weak scaling: every GPU owns a 16384^2 tile of a
 periodic Py x Px Cartesian grid (1x1, 1x2, 2x2, 2x4); one step = one Jacobi
 sweep of every tile INCLUDING the halo exchange, which is fused into the same
 kernel (peer stores over NVLink + device-side epoch flags).  By default the kernel is the
-temporally blocked one (``--temporal 2``): every sweep over the grid advances TWO time steps
-(ghost width 2, corners exchanged), bit-identical to two single steps, so the grid is read
-and written once per two updates; the JSON also carries the ``--temporal 1`` number.
+temporally blocked one (``--temporal 3``): every sweep over the grid advances THREE time steps
+(ghost width 3, corners exchanged), bit-identical to three single steps, so the grid is read
+and written once per three updates; the JSON also carries the ``--temporal 1`` number.
 
     python bench.py --gpus 1 --steps 20 --warmup 3
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
@@ -39,9 +39,9 @@ def parse_args(argv=None):
     ap.add_argument("--tile", type=int, default=16384, help="cells per side of each GPU's tile")
     ap.add_argument("--radius", type=int, default=1)
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--temporal", type=int, default=0, choices=[0, 1, 2],
-                    help="time steps per kernel sweep: 2 = temporal blocking (radius 1 only), "
-                         "1 = one step per sweep, 0 = 2 where possible")
+    ap.add_argument("--temporal", type=int, default=0, choices=[0, 1, 2, 3, 4],
+                    help="time steps per kernel sweep: 2-4 = temporal blocking (radius 1 only), "
+                         "1 = one step per sweep, 0 = 3 where possible")
     ap.add_argument("--th", type=int, default=0, help="explicit per-GPU tile height (experiments)")
     ap.add_argument("--tw", type=int, default=0, help="explicit per-GPU tile width (experiments)")
     return ap.parse_args(argv)
@@ -85,8 +85,8 @@ def main(argv=None) -> int:
     if args.th and args.tw:
         th, tw = args.th, args.tw
     R = args.radius
-    T = args.temporal or (2 if R == 1 else 1)
-    args.steps += args.steps % T              # whole sweeps only; the JSON reports what was run
+    T = args.temporal or (3 if R == 1 else 1)
+    args.steps += (-args.steps) % T           # whole sweeps only; the JSON reports what was run
     coeffs = jacobi_coeffs(R)
 
     def make_plan(temporal):

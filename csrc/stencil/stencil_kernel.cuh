@@ -71,11 +71,11 @@ __host__ __device__ constexpr size_t land_index(int padded_row, int g, int R) {
 // directions with a column (east/west) component: NW NE W E SW SE
 constexpr unsigned kColDirs = (1u << 0) | (1u << 2) | (1u << 3) | (1u << 4) | (1u << 5) | (1u << 7);
 
-template <int R>
+template <int R, int TH = kTileH>
 struct Geo {
     static constexpr int RA = (R + 1) & ~1;  // column halo rounded up to 16 B
     static constexpr int BOXW = kTileW + 2 * RA;
-    static constexpr int BOXH = kTileH + 2 * R;
+    static constexpr int BOXH = TH + 2 * R;
     static constexpr int BOX_BYTES = BOXW * BOXH * 8;
     static constexpr int STAGE_BYTES = (BOX_BYTES + 127) & ~127;
 };
@@ -155,20 +155,27 @@ __device__ __forceinline__ unsigned active_dirs(const LaunchParams& P, unsigned 
     return a;
 }
 
-// TB2 (temporal blocking, two time steps per sweep): the geometry, halo width and the
-// whole exchange protocol are those of R = 2 with corners, but the arithmetic is a
-// radius-1 star applied TWICE: each thread first forms the intermediate time level for its
-// two columns plus one column on either side from the shared-memory box (rows slide through
-// registers), then the second level from those registers.  One sweep reads and writes the
-// grid once for two updates, so the DRAM roofline is 8 bytes per cell update instead of 16.
-// Every value is computed with the same operation order as two single steps would use, on
-// this GPU or on the neighbour that owns the cell, so results stay bit-identical.
-template <int R, bool BOX, bool RESID, int NSTAGES, bool TB2 = false>
-__global__ void __launch_bounds__(kThreads, (NSTAGES <= 3 && R <= 2 && !TB2) ? 2 : 1)
+// TB (temporal blocking, TB = R time steps per sweep): the geometry, halo width and the whole
+// exchange protocol are those of radius R with corners, but the arithmetic is a radius-1 star
+// applied R times.  Each thread slides three input rows through registers and forms time level
+// k for its two columns plus R-k columns on either side (rows likewise), level k+1 from the
+// registers of level k; nothing intermediate touches shared or global memory and no barrier
+// separates the levels.  One sweep reads and writes the grid once for R updates, so the DRAM
+// roofline is 16/R bytes per cell update.  Every value is computed with the same operation order
+// as single steps would use, on this GPU or on the neighbour that owns the cell, so results stay
+// bit-identical.
+// TH: output rows per tile (a multiple of 4; every consumer thread owns TH/4 rows of two
+// columns).  Taller tiles cut the redundant rows of the temporally blocked variants
+// (TB = 3: 8.0 -> 7.0 cell updates per output cell) at the price of a shallower ring.
+template <int R, bool BOX, bool RESID, int NSTAGES, int TB = 0, int TH = B2C_TILE_H>
+__global__ void __launch_bounds__(kThreads, (NSTAGES <= 3 && R <= 2 && TB == 0) ? 2 : 1)
 stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                      const __grid_constant__ LaunchParams P) {
-    static_assert(!TB2 || (R == 2 && !BOX), "temporal blocking: radius-1 star on the R = 2 geometry");
-    using G = Geo<R>;
+    static_assert(TB == 0 || (TB == R && R >= 2 && !BOX), "temporal blocking: radius-1 star, R levels");
+    static_assert(TH % 4 == 0 && TH >= 4 * kMaxRadius, "tile height: 4 row bands");
+    constexpr int kTileH = TH;               // shadow the namespace-level defaults
+    constexpr int kRowsPerThread = TH / 4;
+    using G = Geo<R, TH>;
     extern __shared__ __align__(128) unsigned char smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + NSTAGES * G::STAGE_BYTES);
     uint64_t* empty = full + NSTAGES;
@@ -236,7 +243,7 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
     }
 
     // =============================== consumers ===============================
-    constexpr int NCOEF = TB2 ? 5 : (BOX ? (2 * R + 1) * (2 * R + 1) : 4 * R + 1);
+    constexpr int NCOEF = TB ? 5 : (BOX ? (2 * R + 1) * (2 * R + 1) : 4 * R + 1);
     double c[NCOEF];
 #pragma unroll
     for (int k = 0; k < NCOEF; ++k) c[k] = __ldg(P.coef + k);
@@ -279,61 +286,66 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
         const double* mycol = box + c0 + G::RA;
 
         double2 res[kRowsPerThread];
-        if constexpr (TB2) {
-            // in[]: three consecutive input rows, columns c0-2 .. c0+3 (three 16-byte loads
-            // per row); mid[]: three consecutive rows of the intermediate level, columns
-            // c0-1 .. c0+2.  Output row y needs intermediate rows y-1, y, y+1, which need input
-            // rows y-2 .. y+2: box rows r0 .. r0 + kRowsPerThread + 3.
-            double in[3][6], mid[3][4];
-            auto load_row = [&](double (&dst)[6], int box_row) {
-                const double* p = mycol + box_row * G::BOXW - 2;
+        if constexpr (TB != 0) {
+            // lv[0]: input rows (aligned columns c0-RA .. c0+1+RA); lv[k], k = 1..TB-1: time level k
+            // at columns c0-(TB-k) .. c0+1+(TB-k).  Index [2] is the newest row of each window.
+            // Input row j (box row r0 + j) lets level k produce its row r0 - TB + j - k once
+            // j >= 2k; level TB (the output) starts at j = 2 TB with tile row r0.
+            constexpr int LW = 2 * G::RA + 2;
+            double lv[TB][3][LW];
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const double2 v = *reinterpret_cast<const double2*>(p + 2 * k);
-                    dst[2 * k] = v.x;
-                    dst[2 * k + 1] = v.y;
-                }
-            };
-            load_row(in[0], r0);
-            load_row(in[1], r0 + 1);
+            for (int j = 0; j < kRowsPerThread + 2 * TB; ++j) {
+                {
+                    const double* p = mycol + (r0 + j) * G::BOXW - G::RA;
 #pragma unroll
-            for (int j = 0; j < kRowsPerThread + 2; ++j) {
-                load_row(in[2], r0 + j + 2);
-                // intermediate row (tile row r0 - 1 + j) at columns c0-1 .. c0+2
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    double a = c[0] * in[1][k + 1];
-                    a = fma(c[1], in[1][k], a);          // west
-                    a = fma(c[2], in[1][k + 2], a);      // east
-                    a = fma(c[3], in[0][k + 1], a);      // north
-                    a = fma(c[4], in[2][k + 1], a);      // south
-                    mid[2][k] = a;
-                }
-                if (j >= 2) {
-                    const int y = j - 2;
-                    double ax = c[0] * mid[1][1], ay = c[0] * mid[1][2];
-                    ax = fma(c[1], mid[1][0], ax);
-                    ay = fma(c[1], mid[1][1], ay);
-                    ax = fma(c[2], mid[1][2], ax);
-                    ay = fma(c[2], mid[1][3], ay);
-                    ax = fma(c[3], mid[0][1], ax);
-                    ay = fma(c[3], mid[0][2], ay);
-                    ax = fma(c[4], mid[2][1], ax);
-                    ay = fma(c[4], mid[2][2], ay);
-                    res[y] = make_double2(ax, ay);
-                    if constexpr (RESID) {   // residual of the SECOND of the two updates
-                        const int gy = ty * kTileH + r0 + y, gx = tx * kTileW + c0;
-                        if (gy < P.H && gx < P.W) {
-                            const double dx_ = ax - mid[1][1], dy_ = ay - mid[1][2];
-                            racc = fma(dx_, dx_, racc);
-                            racc = fma(dy_, dy_, racc);
-                        }
+                    for (int k = 0; k < LW / 2; ++k) {
+                        const double2 v = *reinterpret_cast<const double2*>(p + 2 * k);
+                        lv[0][2][2 * k] = v.x;
+                        lv[0][2][2 * k + 1] = v.y;
                     }
                 }
 #pragma unroll
-                for (int k = 0; k < 6; ++k) { in[0][k] = in[1][k]; in[1][k] = in[2][k]; }
+                for (int k = 1; k <= TB; ++k) {
+                    if (j < 2 * k) continue;
+                    // column i of level k is tile column c0 - (TB-k) + i; its west neighbour in
+                    // level k-1 has index i + off, centre i + off + 1, east i + off + 2
+                    const int off = (k == 1) ? G::RA - TB : 0;
+                    const int ncol = 2 + 2 * (TB - k);
+                    double outv[2 + 2 * TB];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { mid[0][k] = mid[1][k]; mid[1][k] = mid[2][k]; }
+                    for (int i = 0; i < ncol; ++i) {
+                        double a = c[0] * lv[k - 1][1][i + off + 1];
+                        a = fma(c[1], lv[k - 1][1][i + off], a);          // west
+                        a = fma(c[2], lv[k - 1][1][i + off + 2], a);      // east
+                        a = fma(c[3], lv[k - 1][0][i + off + 1], a);      // north
+                        a = fma(c[4], lv[k - 1][2][i + off + 1], a);      // south
+                        outv[i] = a;
+                    }
+                    if (k < TB) {
+#pragma unroll
+                        for (int i = 0; i < ncol; ++i) lv[k][2][i] = outv[i];
+                    } else {
+                        const int y = j - 2 * TB;
+                        res[y] = make_double2(outv[0], outv[1]);
+                        if constexpr (RESID) {   // residual of the LAST of the TB updates
+                            const int gy = ty * kTileH + r0 + y, gx = tx * kTileW + c0;
+                            if (gy < P.H && gx < P.W) {
+                                const int o1 = (TB == 1) ? G::RA - TB : 0;
+                                const double dx_ = outv[0] - lv[TB - 1][1][o1 + 1];
+                                const double dy_ = outv[1] - lv[TB - 1][1][o1 + 2];
+                                racc = fma(dx_, dx_, racc);
+                                racc = fma(dy_, dy_, racc);
+                            }
+                        }
+                    }
+                }
+                // slide every window that received a row in this iteration
+#pragma unroll
+                for (int k = 0; k < TB; ++k) {
+                    if (j < 2 * k) continue;
+#pragma unroll
+                    for (int i = 0; i < LW; ++i) { lv[k][0][i] = lv[k][1][i]; lv[k][1][i] = lv[k][2][i]; }
+                }
             }
         } else if constexpr (!BOX) {
             double2 win[2 * R + 1];

@@ -206,6 +206,7 @@ struct Plan {
     size_t smem;
     uint64_t timeout_ns;
     int tilesX, tilesY;
+    int tile_h;                  // output rows per kernel tile (kTileH; 64 for 3-4 levels per sweep)
     uint64_t contrib[8];         // signals per step a neighbour sends me per direction
     unsigned long long launches; // kernels launched through this plan (for bench accounting)
     // ---- strip kernel (algo 1) ----
@@ -381,9 +382,9 @@ static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, c
     B200_CHECK_LAUNCH();
 }
 
-template <int R, bool BOX, bool RESID, int NST, bool TB2 = false>
+template <int R, bool BOX, bool RESID, int NST, int TB = 0, int TH = kTileH>
 static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) {
-    auto k = stencil_fused_kernel<R, BOX, RESID, NST, TB2>;
+    auto k = stencil_fused_kernel<R, BOX, RESID, NST, TB, TH>;
     static bool attr_done[64] = {};
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -406,29 +407,37 @@ static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStr
     else launch_one<R, BOX, false, NST>(pl, lp, st);
 }
 
-// kind 2: radius-1 star, two time steps per sweep, on the R = 2 geometry
-static void launch_tb2(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+// kind 2: radius-1 star, R time steps per sweep, on the radius-R geometry
+template <int T>
+static void launch_tb(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.tile_h == 64) {             // tall tiles: two stages is all that fits
+        if (resid) launch_one<T, false, true, 2, T, 64>(pl, lp, st);
+        else launch_one<T, false, false, 2, T, 64>(pl, lp, st);
+        return;
+    }
     switch (pl.nstages) {
         case 2:
-            if (resid) launch_one<2, false, true, 2, true>(pl, lp, st);
-            else launch_one<2, false, false, 2, true>(pl, lp, st);
+            if (resid) launch_one<T, false, true, 2, T>(pl, lp, st);
+            else launch_one<T, false, false, 2, T>(pl, lp, st);
             return;
         case 4:
-            if (resid) launch_one<2, false, true, 4, true>(pl, lp, st);
-            else launch_one<2, false, false, 4, true>(pl, lp, st);
-            return;
-        case 5:
-            if (resid) launch_one<2, false, true, 5, true>(pl, lp, st);
-            else launch_one<2, false, false, 5, true>(pl, lp, st);
+            if (resid) launch_one<T, false, true, 4, T>(pl, lp, st);
+            else launch_one<T, false, false, 4, T>(pl, lp, st);
             return;
         default:
-            if (resid) launch_one<2, false, true, 3, true>(pl, lp, st);
-            else launch_one<2, false, false, 3, true>(pl, lp, st);
+            if (resid) launch_one<T, false, true, 3, T>(pl, lp, st);
+            else launch_one<T, false, false, 3, T>(pl, lp, st);
     }
 }
 
 static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
-    if (pl.kind == 2) { launch_tb2(pl, lp, resid, st); return; }
+    if (pl.kind == 2) {
+        switch (pl.L.R) {
+            case 2: launch_tb<2>(pl, lp, resid, st); return;
+            case 3: launch_tb<3>(pl, lp, resid, st); return;
+            case 4: launch_tb<4>(pl, lp, resid, st); return;
+        }
+    }
     if (pl.algo == 1) {
         if (pl.L.R == 1) launch_strip<1>(pl, lp, resid, st);
         else launch_strip<2>(pl, lp, resid, st);
@@ -497,9 +506,9 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
                                   void* local_base, void* const nbr_base[8], int push_corners) {
     B2C_TRY
     B200_REQUIRE(out && local_base, ERR_ARG, "null argument");
-    B200_REQUIRE(kind == 0 || (kind == 1 && R <= 2) || (kind == 2 && R == 2), ERR_ARG,
-                 "kind must be 0 (star, R<=4), 1 (box, R<=2) or 2 (radius-1 star x 2 time steps "
-                 "per sweep; pass R = 2, the ghost width)");
+    B200_REQUIRE(kind == 0 || (kind == 1 && R <= 2) || (kind == 2 && R >= 2), ERR_ARG,
+                 "kind must be 0 (star, R<=4), 1 (box, R<=2) or 2 (radius-1 star x R time steps "
+                 "per sweep, R = 2..4 = the ghost width)");
     b2c_stencil_layout_t tmp;
     int rc = b2c_stencil_layout(W, H, R, &tmp);
     if (rc) return rc;
@@ -513,13 +522,21 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
     B200_CHECK_CUDA(cudaGetDevice(&p.device));
     p.base = static_cast<unsigned char*>(local_base);
     for (int d = 0; d < 8; ++d) p.nbr[d] = static_cast<unsigned char*>(nbr_base ? nbr_base[d] : nullptr);
+    p.tile_h = kTileH;
+    if (kind == 2 && kTileH == 32) {
+        // 3 or 4 time levels per sweep are compute bound: 64-row tiles (16 rows per thread) do
+        // 7.0 instead of 8.0 cell updates per output cell for 3 levels (846 vs 790 Gcell/s)
+        const char* he = std::getenv("B2C_TB_TILE_H");
+        p.tile_h = he ? (std::atoi(he) == 64 ? 64 : 32) : (R >= 3 ? 64 : 32);
+        if (!(H % p.tile_h == 0 || H % p.tile_h >= R)) p.tile_h = 32;   // edge strip must not straddle tiles
+    }
     p.tilesX = (W + kTileW - 1) / kTileW;
-    p.tilesY = (H + kTileH - 1) / kTileH;
+    p.tilesY = (H + p.tile_h - 1) / p.tile_h;
     p.timeout_ns = 20ull * 1000 * 1000 * 1000;
 
     // shared memory / grid
     const int RA = (R + 1) & ~1;
-    const size_t stage = (((size_t)(kTileW + 2 * RA) * (kTileH + 2 * R) * 8) + 127) & ~(size_t)127;
+    const size_t stage = (((size_t)(kTileW + 2 * RA) * (p.tile_h + 2 * R) * 8) + 127) & ~(size_t)127;
     p.nstages = R <= 2 ? 3 : 4;
     p.ctas_per_sm = R <= 2 ? 2 : 1;
     {
@@ -539,10 +556,11 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
     }
     if (const char* te = std::getenv("B2C_TILE_STAGES")) {
         const int v = std::atoi(te);
-        if (R <= 2 && (v == 2 || v == 3 || (kind == 2 && (v == 4 || v == 5)))) p.nstages = v;
+        if ((R <= 2 && (v == 2 || v == 3)) || (kind == 2 && v >= 2 && v <= 4)) p.nstages = v;
     }
     if (const char* ce = std::getenv("B2C_TILE_CTAS_PER_SM"))
         if (R <= 2 && kind != 2 && (std::atoi(ce) == 1 || std::atoi(ce) == 2)) p.ctas_per_sm = std::atoi(ce);
+    if (p.tile_h == 64) p.nstages = 2;
     p.smem = p.nstages * stage + 2 * p.nstages * sizeof(uint64_t);
     cudaDeviceProp prop;
     B200_CHECK_CUDA(cudaGetDeviceProperties(&prop, p.device));
@@ -555,7 +573,7 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
     for (int b = 0; b < 2; ++b) {
         cuuint64_t gdim[2] = {(cuuint64_t)p.L.pitch, (cuuint64_t)p.L.rows};
         cuuint64_t gstr[1] = {(cuuint64_t)p.L.pitch * sizeof(double)};
-        cuuint32_t box[2] = {(cuuint32_t)(kTileW + 2 * RA), (cuuint32_t)(kTileH + 2 * R)};
+        cuuint32_t box[2] = {(cuuint32_t)(kTileW + 2 * RA), (cuuint32_t)(p.tile_h + 2 * R)};
         cuuint32_t estr[2] = {1, 1};
         const char* pe = std::getenv("B2C_STENCIL_L2PROMO");
         const int promo = pe ? std::atoi(pe) : 128;

@@ -50,9 +50,9 @@ def layout(W: int, H: int, radius: int) -> _lib.StencilLayout:
 def _check_temporal(radius: int, kind: str, periods, temporal: int) -> None:
     if temporal == 1:
         return
-    if temporal != 2 or kind != "star" or radius != 1 or not all(bool(p) for p in periods):
-        raise ValueError("temporal blocking supports temporal=2 with a radius-1 star stencil on a "
-                         "fully periodic grid")
+    if temporal not in (2, 3, 4) or kind != "star" or radius != 1 or not all(bool(p) for p in periods):
+        raise ValueError("temporal blocking supports temporal=2, 3 or 4 with a radius-1 star stencil "
+                         "on a fully periodic grid")
 
 
 def _stream_ptr(device: int) -> int:
@@ -82,7 +82,7 @@ class Stencil2D:
         h = C.c_void_p()
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_create(C.byref(h), self.W, self.H, radius * self.temporal,
-                                                   2 if self.temporal == 2 else KIND[kind],
+                                                   2 if self.temporal > 1 else KIND[kind],
                                                    C.c_void_p(symbuf.local_ptr), C.byref(nbr),
                                                    int(push_corners)))
         self._h = h
@@ -99,10 +99,10 @@ class Stencil2D:
                push_corners: bool = True, temporal: int = 1) -> "Stencil2D":
         """Collective over ``world``: every rank gets an ``H x W`` tile.
 
-        ``temporal=2`` (radius-1 star on a fully periodic grid): temporal blocking -- every
-        sweep of the fused kernel advances TWO time steps from one read and one write of the
-        grid (ghost width 2, corners exchanged), bit-identical to two single steps.
-        :meth:`step` then takes an even number of steps."""
+        ``temporal=T`` with T = 2, 3 or 4 (radius-1 star on a fully periodic grid): temporal
+        blocking -- every sweep of the fused kernel advances T time steps from one read and one
+        write of the grid (ghost width T, corners exchanged), bit-identical to T single steps.
+        :meth:`step` then takes a multiple of T steps."""
         dims = tuple(dims) if dims is not None else dims_create(world.size, 2)
         cart = CartTopology.create(dims, periods)
         if cart.size != world.size:

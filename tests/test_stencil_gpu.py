@@ -139,14 +139,15 @@ def test_both_kernels_agree_bitwise_and_match_oracle(monkeypatch, algo, dims, ti
     assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
 
 
+@pytest.mark.parametrize("T", [2, 3, 4])
 @pytest.mark.parametrize("dims,tile_hw", [((1, 1), (96, 384)), ((2, 2), (64, 256)), ((2, 4), (40, 504)),
                                           ((3, 3), (32, 260)), ((1, 2), (50, 200)), ((1, 1), (256, 1024))])
-def test_temporal_blocking_is_bit_identical_to_single_steps(dims, tile_hw):
-    """temporal=2: one sweep = two time steps (ghost width 2, corners exchanged).  Same bits as
+def test_temporal_blocking_is_bit_identical_to_single_steps(dims, tile_hw, T):
+    """temporal=T: one sweep = T time steps (ghost width T, corners exchanged).  Same bits as
     the single-step kernel, same residual (of the last update), complete ghost ring."""
-    steps = 6
+    steps = 12
     coeffs = [0.1, 0.2, 0.25, 0.15, 0.3]
-    tb, glob = _run_group(dims, tile_hw, 1, "star", steps, coeffs, temporal=2)
+    tb, glob = _run_group(dims, tile_hw, 1, "star", steps, coeffs, temporal=T)
     one, _ = _run_group(dims, tile_hw, 1, "star", steps, coeffs)
     got = tb.gather_global()
     assert torch.equal(got, one.gather_global())
@@ -156,12 +157,12 @@ def test_temporal_blocking_is_bit_identical_to_single_steps(dims, tile_hw):
     assert torch.allclose(got, exp, rtol=1e-12, atol=1e-13)
     assert tb.residual() == pytest.approx(one.residual(), rel=1e-12)
     s = tb.ranks[0]
-    assert s.steps_done == steps and s.layout.ghost == 2
-    ri = (torch.arange(-2, tile_hw[0] + 2)) % exp.shape[0]
-    ci = (torch.arange(-2, tile_hw[1] + 2)) % exp.shape[1]
+    assert s.steps_done == steps and s.layout.ghost == T
+    ri = (torch.arange(-T, tile_hw[0] + T)) % exp.shape[0]
+    ci = (torch.arange(-T, tile_hw[1] + T)) % exp.shape[1]
     assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
     with pytest.raises(ValueError):
-        s.step(3)
+        s.step(T + 1)
 
 
 def test_temporal_blocking_rejects_what_it_cannot_do():
@@ -173,25 +174,26 @@ def test_temporal_blocking_rejects_what_it_cannot_do():
         Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 1, "box", dims=(1, 1), temporal=2)
 
 
-def test_temporal_blocking_graph_replay():
+@pytest.mark.parametrize("T", [2, 3])
+def test_temporal_blocking_graph_replay(T):
     hw = (96, 512)
-    plain, glob = _run_group((1, 1), hw, 1, "star", 14)
-    grp = Stencil2D.create_group(cms.LocalGroup(1), hw, 1, "star", dims=(1, 1), temporal=2)
+    plain, glob = _run_group((1, 1), hw, 1, "star", 7 * T)
+    grp = Stencil2D.create_group(cms.LocalGroup(1), hw, 1, "star", dims=(1, 1), temporal=T)
     s = grp.ranks[0]
     s.fill(0.0, 0.0)
     grp.scatter_global(glob)
     grp.exchange()
-    s.step(2)
+    s.step(T)
     torch.cuda.synchronize()
-    graph = s.capture(4)
+    graph = s.capture(2 * T)
     for _ in range(3):
         graph.replay()
     torch.cuda.synchronize()
     s.check()
-    assert s.steps_done == 14
+    assert s.steps_done == 7 * T
     assert torch.equal(grp.gather_global(), plain.gather_global())
     with pytest.raises(ValueError):
-        s.capture(2)
+        s.capture(T)
 
 
 def test_missing_neighbour_times_out_instead_of_hanging():
