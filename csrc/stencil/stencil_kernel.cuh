@@ -167,11 +167,15 @@ __device__ __forceinline__ unsigned active_dirs(const LaunchParams& P, unsigned 
 // TH: output rows per tile (a multiple of 4; every consumer thread owns TH/4 rows of two
 // columns).  Taller tiles cut the redundant rows of the temporally blocked variants
 // (TB = 3: 8.0 -> 7.0 cell updates per output cell) at the price of a shallower ring.
-template <int R, bool BOX, bool RESID, int NSTAGES, int TB = 0, int TH = B2C_TILE_H>
+// LV: time levels actually computed by this sweep (1 <= LV <= TB).  LV < TB is the partial sweep
+// that ends a run whose step count is not a multiple of TB: same geometry and exchange, fewer
+// levels.
+template <int R, bool BOX, bool RESID, int NSTAGES, int TB = 0, int TH = B2C_TILE_H, int LV = TB>
 __global__ void __launch_bounds__(kThreads, (NSTAGES <= 3 && R <= 2 && TB == 0) ? 2 : 1)
 stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                      const __grid_constant__ LaunchParams P) {
     static_assert(TB == 0 || (TB == R && R >= 2 && !BOX), "temporal blocking: radius-1 star, R levels");
+    static_assert(TB == 0 ? LV == 0 : (LV >= 1 && LV <= TB), "levels per sweep");
     static_assert(TH % 4 == 0 && TH >= 4 * kMaxRadius, "tile height: 4 row bands");
     constexpr int kTileH = TH;               // shadow the namespace-level defaults
     constexpr int kRowsPerThread = TH / 4;
@@ -287,16 +291,16 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
 
         double2 res[kRowsPerThread];
         if constexpr (TB != 0) {
-            // lv[0]: input rows (aligned columns c0-RA .. c0+1+RA); lv[k], k = 1..TB-1: time level k
-            // at columns c0-(TB-k) .. c0+1+(TB-k).  Index [2] is the newest row of each window.
-            // Input row j (box row r0 + j) lets level k produce its row r0 - TB + j - k once
-            // j >= 2k; level TB (the output) starts at j = 2 TB with tile row r0.
+            // lv[0]: input rows (aligned columns c0-RA .. c0+1+RA); lv[k], k = 1..LV-1: time level k
+            // at columns c0-(LV-k) .. c0+1+(LV-k).  Index [2] is the newest row of each window.
+            // Input row j (tile row r0 - LV + j) lets level k produce its row r0 - LV + j - k once
+            // j >= 2k; level LV (the output) starts at j = 2 LV with tile row r0.
             constexpr int LW = 2 * G::RA + 2;
-            double lv[TB][3][LW];
+            double lv[LV][3][LW];
 #pragma unroll
-            for (int j = 0; j < kRowsPerThread + 2 * TB; ++j) {
+            for (int j = 0; j < kRowsPerThread + 2 * LV; ++j) {
                 {
-                    const double* p = mycol + (r0 + j) * G::BOXW - G::RA;
+                    const double* p = mycol + (r0 + (R - LV) + j) * G::BOXW - G::RA;
 #pragma unroll
                     for (int k = 0; k < LW / 2; ++k) {
                         const double2 v = *reinterpret_cast<const double2*>(p + 2 * k);
@@ -305,13 +309,13 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                     }
                 }
 #pragma unroll
-                for (int k = 1; k <= TB; ++k) {
+                for (int k = 1; k <= LV; ++k) {
                     if (j < 2 * k) continue;
-                    // column i of level k is tile column c0 - (TB-k) + i; its west neighbour in
+                    // column i of level k is tile column c0 - (LV-k) + i; its west neighbour in
                     // level k-1 has index i + off, centre i + off + 1, east i + off + 2
-                    const int off = (k == 1) ? G::RA - TB : 0;
-                    const int ncol = 2 + 2 * (TB - k);
-                    double outv[2 + 2 * TB];
+                    const int off = (k == 1) ? G::RA - LV : 0;
+                    const int ncol = 2 + 2 * (LV - k);
+                    double outv[2 + 2 * LV];
 #pragma unroll
                     for (int i = 0; i < ncol; ++i) {
                         double a = c[0] * lv[k - 1][1][i + off + 1];
@@ -321,18 +325,18 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                         a = fma(c[4], lv[k - 1][2][i + off + 1], a);      // south
                         outv[i] = a;
                     }
-                    if (k < TB) {
+                    if (k < LV) {
 #pragma unroll
                         for (int i = 0; i < ncol; ++i) lv[k][2][i] = outv[i];
                     } else {
-                        const int y = j - 2 * TB;
+                        const int y = j - 2 * LV;
                         res[y] = make_double2(outv[0], outv[1]);
-                        if constexpr (RESID) {   // residual of the LAST of the TB updates
+                        if constexpr (RESID) {   // residual of the LAST of the LV updates
                             const int gy = ty * kTileH + r0 + y, gx = tx * kTileW + c0;
                             if (gy < P.H && gx < P.W) {
-                                const int o1 = (TB == 1) ? G::RA - TB : 0;
-                                const double dx_ = outv[0] - lv[TB - 1][1][o1 + 1];
-                                const double dy_ = outv[1] - lv[TB - 1][1][o1 + 2];
+                                const int o1 = (LV == 1) ? G::RA - LV : 0;
+                                const double dx_ = outv[0] - lv[LV - 1][1][o1 + 1];
+                                const double dy_ = outv[1] - lv[LV - 1][1][o1 + 2];
                                 racc = fma(dx_, dx_, racc);
                                 racc = fma(dy_, dy_, racc);
                             }
@@ -341,7 +345,7 @@ stencil_fused_kernel(const __grid_constant__ CUtensorMap tmap_in,
                 }
                 // slide every window that received a row in this iteration
 #pragma unroll
-                for (int k = 0; k < TB; ++k) {
+                for (int k = 0; k < LV; ++k) {
                     if (j < 2 * k) continue;
 #pragma unroll
                     for (int i = 0; i < LW; ++i) { lv[k][0][i] = lv[k][1][i]; lv[k][1][i] = lv[k][2][i]; }

@@ -207,6 +207,7 @@ struct Plan {
     uint64_t timeout_ns;
     int tilesX, tilesY;
     int tile_h;                  // output rows per kernel tile (kTileH; 64 for 3-4 levels per sweep)
+    int partial_levels;          // kind 2: levels of the NEXT sweep if fewer than R (0 = all)
     uint64_t contrib[8];         // signals per step a neighbour sends me per direction
     unsigned long long launches; // kernels launched through this plan (for bench accounting)
     // ---- strip kernel (algo 1) ----
@@ -382,9 +383,9 @@ static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, c
     B200_CHECK_LAUNCH();
 }
 
-template <int R, bool BOX, bool RESID, int NST, int TB = 0, int TH = kTileH>
+template <int R, bool BOX, bool RESID, int NST, int TB = 0, int TH = kTileH, int LV = TB>
 static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) {
-    auto k = stencil_fused_kernel<R, BOX, RESID, NST, TB, TH>;
+    auto k = stencil_fused_kernel<R, BOX, RESID, NST, TB, TH, LV>;
     static bool attr_done[64] = {};
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -408,8 +409,26 @@ static void launch_r(const Plan& pl, const LaunchParams& lp, bool resid, cudaStr
 }
 
 // kind 2: radius-1 star, R time steps per sweep, on the radius-R geometry
+// Partial sweep (LV < T levels): rare (at most once per step() call), so only the 2-stage
+// instantiation exists -- every plan allocates at least two stages of shared memory.
+template <int T, int LV>
+static void launch_tb_partial(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.tile_h == 64) {
+        if (resid) launch_one<T, false, true, 2, T, 64, LV>(pl, lp, st);
+        else launch_one<T, false, false, 2, T, 64, LV>(pl, lp, st);
+    } else {
+        if (resid) launch_one<T, false, true, 2, T, kTileH, LV>(pl, lp, st);
+        else launch_one<T, false, false, 2, T, kTileH, LV>(pl, lp, st);
+    }
+}
+
 template <int T>
 static void launch_tb(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.partial_levels > 0 && pl.partial_levels < T) {
+        if constexpr (T >= 2) if (pl.partial_levels == 1) { launch_tb_partial<T, 1>(pl, lp, resid, st); return; }
+        if constexpr (T >= 3) if (pl.partial_levels == 2) { launch_tb_partial<T, 2>(pl, lp, resid, st); return; }
+        if constexpr (T >= 4) if (pl.partial_levels == 3) { launch_tb_partial<T, 3>(pl, lp, resid, st); return; }
+    }
     if (pl.tile_h == 64) {             // tall tiles: two stages is all that fits
         if (resid) launch_one<T, false, true, 2, T, 64>(pl, lp, st);
         else launch_one<T, false, false, 2, T, 64>(pl, lp, st);
@@ -795,6 +814,20 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         p.launches += 1;
     }
     if (flags & 2) p.launches += drain_impl(p, false, st);
+    B2C_CATCH
+}
+
+// kind 2 only: ONE sweep that computes `levels` (1 .. R) time levels instead of all R -- the
+// tail of a run whose step count is not a multiple of R.  Same exchange, same epochs.
+B2C_EXPORT int b2c_stencil_step_levels(b2c_stencil* h, int levels, int flags, void* stream) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null plan");
+    B200_REQUIRE(h->p.kind == 2 && levels >= 1 && levels <= h->p.L.R, ERR_ARG,
+                 "levels must be in [1, levels per sweep] of a temporally blocked plan");
+    h->p.partial_levels = levels;
+    const int rc = b2c_stencil_step(h, 1, flags, stream);
+    h->p.partial_levels = 0;
+    return rc;
     B2C_CATCH
 }
 

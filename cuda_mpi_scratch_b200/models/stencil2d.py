@@ -91,6 +91,7 @@ class Stencil2D:
         self._resid_pinned = torch.zeros(1, dtype=torch.float64).pin_memory() \
             if torch.cuda.is_available() else torch.zeros(1, dtype=torch.float64)
         self._graph_launches = 0
+        self._time_steps = 0
 
     # ------------------------------------------------------------ factories
     @classmethod
@@ -102,7 +103,7 @@ class Stencil2D:
         ``temporal=T`` with T = 2, 3 or 4 (radius-1 star on a fully periodic grid): temporal
         blocking -- every sweep of the fused kernel advances T time steps from one read and one
         write of the grid (ghost width T, corners exchanged), bit-identical to T single steps.
-        :meth:`step` then takes a multiple of T steps."""
+        Any step count is accepted: a remainder is done by one partial sweep."""
         dims = tuple(dims) if dims is not None else dims_create(world.size, 2)
         cart = CartTopology.create(dims, periods)
         if cart.size != world.size:
@@ -205,22 +206,32 @@ class Stencil2D:
 
     # ------------------------------------------------------------ stepping
     def step(self, nsteps: int = 1, residual: bool = False, drain: bool = True) -> None:
-        """Enqueue ``nsteps`` fused update+halo steps on the current stream (a multiple of
-        ``temporal``: with temporal blocking one kernel advances two time steps)."""
+        """Enqueue ``nsteps`` fused update+halo time steps on the current stream.  With temporal
+        blocking one kernel sweep advances ``temporal`` steps; a step count that is not a
+        multiple ends with one partial sweep that computes only the remaining levels."""
         flags = (1 if residual else 0) | (2 if drain else 0)
+        L, st = _lib.lib, _stream_ptr(self.device)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib.b2c_stencil_step(self._h, self._sweeps(nsteps), flags,
-                                                 _stream_ptr(self.device)))
+            if self.temporal == 1:
+                _lib.check(L.b2c_stencil_step(self._h, nsteps, flags, st))
+            else:
+                full, rem = divmod(nsteps, self.temporal)
+                if rem == 0:
+                    _lib.check(L.b2c_stencil_step(self._h, full, flags, st))
+                else:
+                    if full:
+                        _lib.check(L.b2c_stencil_step(self._h, full, 0, st))
+                    _lib.check(L.b2c_stencil_step_levels(self._h, rem, flags, st))
+        self._time_steps += nsteps
 
     def _sweeps(self, nsteps: int) -> int:
-        if nsteps % self.temporal:
-            raise ValueError(f"with temporal={self.temporal} the step count must be a multiple of it")
-        return nsteps // self.temporal
+        """Kernel sweeps that :meth:`step` launches for ``nsteps`` time steps."""
+        return -(-nsteps // self.temporal)
 
     @property
     def steps_done(self) -> int:
         """Time steps completed since creation."""
-        return int(self.info().steps_done) * self.temporal
+        return self._time_steps
 
     def drain(self) -> None:
         with torch.cuda.device(self.device):
@@ -232,9 +243,10 @@ class Stencil2D:
         step counter in device memory, so the captured launch parameters stay valid for every
         replay.  Run at least one plain :meth:`step` first (one-time kernel attributes are set
         outside the capture)."""
-        if nsteps <= 0 or nsteps % (2 * self.temporal):
-            raise ValueError("capture a positive number of steps that is a multiple of "
-                             f"{2 * self.temporal} (an even number of kernel sweeps)")
+        if nsteps <= 0 or self._sweeps(nsteps) % 2:
+            raise ValueError("capture a positive number of steps that makes an EVEN number of kernel "
+                             f"sweeps ({self.temporal} step(s) per sweep): the two buffers must end "
+                             "where they started")
         g = torch.cuda.CUDAGraph()
         launches0 = int(self.info().launches)
         side = torch.cuda.Stream(self.device)
@@ -247,6 +259,7 @@ class Stencil2D:
         self._graph_launches -= per_replay      # captured, not executed
         # nothing ran during capture: take the host-side bookkeeping back
         _lib.check(_lib.lib.b2c_stencil_advance(self._h, -self._sweeps(nsteps)))
+        self._time_steps -= nsteps
         return StencilGraph(self, g, nsteps, per_replay)
 
     def local_residual_async(self) -> torch.Tensor:
@@ -284,7 +297,6 @@ class Stencil2D:
         done, res = 0, None
         while done < max_steps:
             n = min(check_every, max_steps - done)
-            n = max(self.temporal, n - n % self.temporal)
             self.step(n, residual=True)
             done += n
             res = self.residual()
@@ -356,6 +368,7 @@ class StencilGraph:
     def replay(self) -> None:
         self.graph.replay()
         _lib.check(_lib.lib.b2c_stencil_advance(self.stencil._h, self.stencil._sweeps(self.nsteps)))
+        self.stencil._time_steps += self.nsteps
         self.stencil._graph_launches += self.launches
 
 
@@ -393,11 +406,11 @@ class StencilGroup:
     def step(self, nsteps: int = 1, residual: bool = False) -> None:
         multi_dev = len({s.device for s in self.ranks}) > 1
         t = self.ranks[0].temporal
-        nsweeps = self.ranks[0]._sweeps(nsteps)
-        for i in range(nsweeps):
-            last = i == nsweeps - 1
+        chunks = [t] * (nsteps // t) + ([nsteps % t] if nsteps % t else [])
+        for i, n in enumerate(chunks):
+            last = i == len(chunks) - 1
             for s in self.ranks:
-                s.step(t, residual=residual and last, drain=False)
+                s.step(n, residual=residual and last, drain=False)
             if multi_dev:
                 # different devices run concurrently: keep ranks within one step
                 # of each other exactly like separate processes would be

@@ -211,7 +211,8 @@ typedef struct {
 /* Neighbour directions: 0 NW, 1 N, 2 NE, 3 W, 4 E, 5 SW, 6 S, 7 SE
  * (the order of MPIGridCellID, stencil2d/stencil2D.h:86-88). */
 int b2c_stencil_layout(int W, int H, int radius, b2c_stencil_layout_t* out);
-int b2c_stencil_create(b2c_stencil** out, int W, int H, int radius, int kind /*0 star,1 box*/,
+int b2c_stencil_create(b2c_stencil** out, int W, int H, int radius,
+                       int kind /*0 star, 1 box, 2 radius-1 star x `radius` time levels per sweep*/,
                        void* local_block, void* const neighbour_block[8], int push_corners);
 int b2c_stencil_destroy(b2c_stencil* s);
 int b2c_stencil_set_coef(b2c_stencil* s, const double* host_coef, int n, void* stream);
@@ -219,6 +220,9 @@ int b2c_stencil_set_timeout_ms(b2c_stencil* s, unsigned long long ms);
 int b2c_stencil_info(b2c_stencil* s, b2c_stencil_info_t* out);
 /* flags: bit0 residual of the last step, bit1 drain the last step's halo */
 int b2c_stencil_step(b2c_stencil* s, int nsteps, int flags, void* stream);
+/* kind 2 (temporal blocking: radius-1 star, `radius` time levels per sweep): one sweep that
+ * computes only `levels` (1..radius) levels -- the tail of a run that is not a multiple */
+int b2c_stencil_step_levels(b2c_stencil* s, int levels, int flags, void* stream);
 /* after replaying a captured CUDA graph of `nsteps` steps: advance the host-side step count */
 int b2c_stencil_advance(b2c_stencil* s, long long nsteps);
 int b2c_stencil_drain(b2c_stencil* s, void* stream);

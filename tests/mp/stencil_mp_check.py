@@ -21,8 +21,8 @@ def main():
     fails = 0
     for (th, tw, R, kind, steps, tb) in [(64, 256, 1, "star", 7, 1), (96, 384, 2, "star", 5, 1),
                                           (50, 200, 1, "box", 4, 1), (1024, 2048, 1, "star", 20, 1),
-                                          (64, 256, 1, "star", 8, 2), (1024, 2048, 1, "star", 20, 2),
-                                          (96, 384, 1, "star", 9, 3), (1024, 2048, 1, "star", 12, 4)]:
+                                          (64, 256, 1, "star", 7, 2), (1024, 2048, 1, "star", 20, 2),
+                                          (96, 384, 1, "star", 11, 3), (1024, 2048, 1, "star", 12, 4)]:
         st = Stencil2D.create(world, (th, tw), R, kind, dims=dims, temporal=tb)
         g = torch.Generator().manual_seed(1234)
         glob = torch.rand(dims[0] * th, dims[1] * tw, dtype=torch.float64, generator=g)
