@@ -33,7 +33,7 @@ def _launch(n, exe, *args, timeout=240):
                           capture_output=True, text=True)
 
 
-@pytest.mark.parametrize("name", ["halo_exchange_gpu", "pingpong_gpu", "dot_gpu"])
+@pytest.mark.parametrize("name", ["halo_exchange_gpu", "pingpong_gpu", "dot_gpu", "stencil_fused_gpu"])
 def test_gpu_drivers_compile_without_a_gpu(name, tmp_path):
     """The GPU drivers (the reference's CUDA main() programs) build against include/ + the library;
     without arguments the ping-pong prints its usage and exits 1 instead of reading a null argv."""
@@ -117,3 +117,18 @@ def test_cpp_halo_driver_reproduces_golden_files(tmp_path):
             ref = open(f"{REF}/{r}_{c}").read()
             ref = re.sub(r"\nCUDA device id: \d+\n", "", ref)     # the CPU driver has no such line
             assert got == ref, f"{r}_{c} differs"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("temporal,steps", [(1, 9), (3, 10), (2, 7), (4, 12)])
+def test_gpu_fused_stencil_driver_from_cpp(tmp_path, temporal, steps):
+    """The flagship through the C++ classes of b200comm/device.hpp (no Python on the path): one
+    rank, periodic 1x1 grid (the rank is its own neighbour in all 8 directions), every cell
+    compared bit for bit with a host computation, partial sweeps included."""
+    import torch
+    exe = _build("stencil_fused_gpu", tmp_path)
+    p = _launch(1, exe, 256, steps, temporal)
+    assert p.returncode == 0 and "PASSED" in p.stdout, p.stdout + p.stderr
+    if torch.cuda.device_count() >= 2:      # one rank per GPU only
+        p = _launch(2, exe, 256, steps, temporal)
+        assert p.returncode == 0 and "PASSED" in p.stdout, p.stdout + p.stderr
