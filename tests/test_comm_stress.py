@@ -4,6 +4,10 @@ them, blocking and non-blocking calls mixed, sub-communicator traffic interleave
 traffic.  Every payload is a function of (source, destination, index), so any mismatch,
 reordering across different tags, truncation or lost message is detected; deadlocks become
 time-outs.  The reference has no such test (its programs are its tests)."""
+import os
+import subprocess
+import sys
+
 import numpy as np
 import pytest
 
@@ -109,3 +113,13 @@ def test_sub_communicator_traffic_does_not_mix_with_world_traffic():
         return True
 
     assert all(cm.run_local(n, body, timeout_s=60.0))
+
+
+@pytest.mark.parametrize("nranks,seed", [(4, 5), (7, 6)])
+def test_random_traffic_between_process_ranks(nranks, seed):
+    """The same schedule with ranks as PROCESSES over the POSIX shared-memory fabric."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, "-m", "cuda_mpi_scratch_b200.launch", "-n", str(nranks), "--timeout", "150",
+                        os.path.join(root, "tests/mp/comm_stress_proc.py"), str(seed)],
+                       cwd=root, capture_output=True, text=True, timeout=240)
+    assert p.returncode == 0 and "COMM_STRESS PASSED" in p.stdout, p.stdout + p.stderr
