@@ -1,7 +1,9 @@
 // mpi.h -- a SHIM, not an MPI implementation.
 //
-// Implements exactly the MPI surface that ugovaretto-accel/cuda-mpi-scratch exercises
-// (~45 functions) on top of the b200comm C ABI, so that the reference's
+// Implements the MPI surface that ugovaretto-accel/cuda-mpi-scratch exercises (SURVEY.md 2.3,
+// ~45 functions) plus the close relatives a program written in that style reaches for next
+// (Sendrecv, Test, Waitany, Iprobe, Allgather, Comm_split/dup, Dims_create, Cart_get, hvector,
+// resized, Get_address, ...) on top of the b200comm C ABI, so that the reference's
 // tutorial sources compile UNCHANGED (`-I include/b200comm/shim`) and run over this
 // library's host transport, launched with `python -m cuda_mpi_scratch_b200.launch -n N`.
 // Purpose: a conformance suite (tests/test_reference_conformance.py builds the sources
@@ -14,6 +16,7 @@
 #ifndef B200COMM_SHIM_MPI_H_
 #define B200COMM_SHIM_MPI_H_
 
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -58,9 +61,16 @@ typedef b2c_shim_group* MPI_Group;
 #define MPI_PROD 1
 #define MPI_MAX 2
 #define MPI_MIN 3
+#define MPI_LAND 4
+#define MPI_LOR 5
+#define MPI_BAND 6
+#define MPI_BOR 7
+#define MPI_VERSION 3
+#define MPI_SUBVERSION 1
 
 namespace b2c_shim {
 inline MPI_Comm world = nullptr;
+inline bool finalized = false;
 inline MPI_Datatype basic(int kind) {
     static MPI_Datatype cache[16] = {};
     if (!cache[kind]) b2c_type_basic(kind, &cache[kind]);
@@ -84,16 +94,33 @@ inline void to_status(MPI_Status* out, const b2c_status& s) {
 #define MPI_DOUBLE (b2c_shim::basic(9))
 #define MPI_DOUBLE_PRECISION (b2c_shim::basic(9))   /* Fortran handle used from C by the reference */
 #define MPI_UNSIGNED (b2c_shim::basic(10))
+#define MPI_SIGNED_CHAR (b2c_shim::basic(2))
+#define MPI_INT8_T (b2c_shim::basic(2))
+#define MPI_UINT8_T (b2c_shim::basic(3))
+#define MPI_INT16_T (b2c_shim::basic(4))
+#define MPI_INT32_T (b2c_shim::basic(5))
+#define MPI_INT64_T (b2c_shim::basic(6))
+#define MPI_UINT64_T (b2c_shim::basic(7))
+#define MPI_UINT32_T (b2c_shim::basic(10))
+#define MPI_LONG (b2c_shim::basic(6))                /* LP64 */
+#define MPI_UNSIGNED_LONG (b2c_shim::basic(7))
+#define MPI_AINT (b2c_shim::basic(6))
 
 // ---- environment ------------------------------------------------------------------
 inline int MPI_Init(int*, char***) { return b2c_init_env(&b2c_shim::world); }
 inline int MPI_Finalize() {
     int rc = b2c_comm_finalize(b2c_shim::world);
     b2c_shim::world = nullptr;
+    b2c_shim::finalized = true;
     return rc;
 }
+inline int MPI_Initialized(int* flag) { *flag = b2c_shim::world != nullptr; return MPI_SUCCESS; }
+inline int MPI_Finalized(int* flag) { *flag = b2c_shim::finalized; return MPI_SUCCESS; }
+inline int MPI_Get_version(int* v, int* sv) { *v = MPI_VERSION; *sv = MPI_SUBVERSION; return MPI_SUCCESS; }
 inline int MPI_Abort(MPI_Comm c, int code) { return b2c_abort(c, code); }
 inline double MPI_Wtime() { return b2c_wtime(); }
+inline double MPI_Wtick() { return 1e-9; }
+inline int MPI_Get_address(const void* p, MPI_Aint* a) { *a = (MPI_Aint)(intptr_t)p; return MPI_SUCCESS; }
 inline int MPI_Get_processor_name(char* name, int* len) {
     int rc = b2c_processor_name(name, MPI_MAX_PROCESSOR_NAME);
     if (len) *len = (int)std::strlen(name);
@@ -131,6 +158,15 @@ inline int MPI_Group_incl(MPI_Group g, int n, const int* ranks, MPI_Group* out) 
     }
     return MPI_SUCCESS;
 }
+inline int MPI_Group_excl(MPI_Group g, int n, const int* ranks, MPI_Group* out) {
+    *out = new b2c_shim_group{g->parent, {}};
+    for (size_t i = 0; i < g->ranks.size(); ++i) {
+        bool drop = false;
+        for (int k = 0; k < n; ++k) drop = drop || ranks[k] == (int)i;
+        if (!drop) (*out)->ranks.push_back(g->ranks[i]);
+    }
+    return MPI_SUCCESS;
+}
 inline int MPI_Group_rank(MPI_Group g, int* rank) {
     int me = 0;
     int rc = b2c_comm_rank(g->parent, &me);
@@ -145,7 +181,40 @@ inline int MPI_Comm_create(MPI_Comm c, MPI_Group g, MPI_Comm* out) {
     return b2c_comm_create(c, (int)g->ranks.size(), g->ranks.data(), out);
 }
 
+inline int MPI_Comm_split(MPI_Comm c, int color, int key, MPI_Comm* out) {
+    return b2c_comm_split(c, color, key, out);     // MPI_UNDEFINED == B2C_UNDEFINED: *out = MPI_COMM_NULL
+}
+inline int MPI_Comm_dup(MPI_Comm c, MPI_Comm* out) { return b2c_comm_dup(c, out); }
+
 // ---- Cartesian topology -------------------------------------------------------------
+inline int MPI_Dims_create(int nnodes, int ndims, int* dims) {
+    // the C ABI returns a balanced factorisation; honour entries the caller fixed (non-zero)
+    int fixed = 1, free_dims = 0;
+    for (int i = 0; i < ndims; ++i) {
+        if (dims[i] > 0) fixed *= dims[i];
+        else ++free_dims;
+    }
+    if (free_dims == 0) return fixed == nnodes ? MPI_SUCCESS : 13;
+    if (nnodes % fixed) return 13;
+    std::vector<int> f((size_t)free_dims);
+    int rc = b2c_dims_create(nnodes / fixed, free_dims, f.data());
+    if (rc) return rc;
+    for (int i = 0, k = 0; i < ndims; ++i)
+        if (dims[i] <= 0) dims[i] = f[(size_t)k++];
+    return MPI_SUCCESS;
+}
+inline int MPI_Cart_get(MPI_Comm c, int maxdims, int* dims, int* periods, int* coords) {
+    int nd = 0, me = 0;
+    int rc = b2c_cart_get(c, maxdims, &nd, dims, periods);
+    if (rc) return rc;
+    rc = b2c_comm_rank(c, &me);
+    if (rc) return rc;
+    return b2c_cart_coords(c, me, maxdims, coords);
+}
+inline int MPI_Cartdim_get(MPI_Comm c, int* ndims) {
+    int d[8], p[8];
+    return b2c_cart_get(c, 8, ndims, d, p);
+}
 inline int MPI_Cart_create(MPI_Comm c, int nd, const int* dims, const int* periods, int reorder,
                            MPI_Comm* out) {
     return b2c_cart_create(c, nd, dims, periods, reorder, out);
@@ -196,6 +265,56 @@ inline int MPI_Waitall(int n, MPI_Request* reqs, MPI_Status* sts) {
     }
     return rc;
 }
+inline int MPI_Test(MPI_Request* r, int* flag, MPI_Status* st) {
+    if (*r == MPI_REQUEST_NULL) { *flag = 1; return MPI_SUCCESS; }
+    b2c_status s{};
+    int rc = b2c_test(*r, flag, &s);
+    if (*flag) {
+        *r = MPI_REQUEST_NULL;
+        b2c_shim::to_status(st, s);
+    }
+    return rc;
+}
+// Completes exactly one active request (polling, like the progress engine underneath).
+inline int MPI_Waitany(int n, MPI_Request* reqs, int* index, MPI_Status* st) {
+    bool any = false;
+    for (int i = 0; i < n; ++i) any = any || reqs[i] != MPI_REQUEST_NULL;
+    *index = MPI_UNDEFINED;
+    if (!any) return MPI_SUCCESS;
+    for (;;) {
+        for (int i = 0; i < n; ++i) {
+            if (reqs[i] == MPI_REQUEST_NULL) continue;
+            int flag = 0;
+            int rc = MPI_Test(&reqs[i], &flag, st);
+            if (rc) return rc;
+            if (flag) { *index = i; return MPI_SUCCESS; }
+        }
+    }
+}
+inline int MPI_Testall(int n, MPI_Request* reqs, int* flag, MPI_Status* sts) {
+    // completes the requests that are done; *flag only when ALL are
+    *flag = 1;
+    for (int i = 0; i < n; ++i) {
+        int f = 0;
+        int rc = MPI_Test(&reqs[i], &f, sts ? &sts[i] : MPI_STATUS_IGNORE);
+        if (rc) return rc;
+        if (!f) *flag = 0;
+    }
+    return MPI_SUCCESS;
+}
+inline int MPI_Sendrecv(const void* sb, int sn, MPI_Datatype st, int dest, int stag, void* rb, int rn,
+                        MPI_Datatype rt, int src, int rtag, MPI_Comm c, MPI_Status* status) {
+    b2c_status s{};
+    int rc = b2c_sendrecv(c, sb, sn, st, dest, stag, rb, rn, rt, src, rtag, &s);
+    b2c_shim::to_status(status, s);
+    return rc;
+}
+inline int MPI_Iprobe(int src, int tag, MPI_Comm c, int* flag, MPI_Status* st) {
+    b2c_status s{};
+    int rc = b2c_iprobe(c, src, tag, flag, &s);
+    if (*flag) b2c_shim::to_status(st, s);
+    return rc;
+}
 inline int MPI_Probe(int src, int tag, MPI_Comm c, MPI_Status* st) {
     b2c_status s{};
     int rc = b2c_probe(c, src, tag, &s);
@@ -228,7 +347,17 @@ inline int MPI_Scatter(const void* s, int sn, MPI_Datatype st, void* r, int rn, 
     return b2c_scatter(c, s, sn, st, r, rn, rt, root);
 }
 
+inline int MPI_Allgather(const void* s, int sn, MPI_Datatype st, void* r, int rn, MPI_Datatype rt, MPI_Comm c) {
+    return b2c_allgather(c, s, sn, st, r, rn, rt);
+}
+
 // ---- datatypes ------------------------------------------------------------------------
+inline int MPI_Type_create_hvector(int n, int bl, MPI_Aint stride, MPI_Datatype old, MPI_Datatype* out) {
+    return b2c_type_hvector(n, bl, stride, old, out);
+}
+inline int MPI_Type_create_resized(MPI_Datatype old, MPI_Aint lb, MPI_Aint extent, MPI_Datatype* out) {
+    return b2c_type_resized(old, lb, extent, out);
+}
 inline int MPI_Type_indexed(int n, const int* bl, const int* disp, MPI_Datatype old, MPI_Datatype* out) {
     return b2c_type_indexed(n, bl, disp, old, out);
 }

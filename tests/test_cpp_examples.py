@@ -132,3 +132,16 @@ def test_gpu_fused_stencil_driver_from_cpp(tmp_path, temporal, steps):
     if torch.cuda.device_count() >= 2:      # one rank per GPU only
         p = _launch(2, exe, 256, steps, temporal)
         assert p.returncode == 0 and "PASSED" in p.stdout, p.stdout + p.stderr
+
+
+def test_mpi_shim_close_relatives(tmp_path):
+    """tests/mp/shim_extra.cpp: an MPI-style program that uses Sendrecv, Test, Waitany, Iprobe,
+    Allgather, logical reductions, Comm_split/dup, Dims_create, Cart_get, hvector + resized types
+    and Get_address through include/b200comm/shim/mpi.h, 4 process ranks."""
+    import cuda_mpi_scratch_b200  # noqa: F401
+    exe = str(tmp_path / "shim_extra")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", f"-I{ROOT}/include/b200comm/shim", f"-I{ROOT}/include",
+                    f"{ROOT}/tests/mp/shim_extra.cpp", "-o", exe, f"-L{LIBDIR}", "-lb200comm",
+                    f"-Wl,-rpath,{LIBDIR}", "-pthread"], check=True, timeout=300)
+    p = _launch(4, exe, timeout=120)
+    assert p.returncode == 0 and "SHIM_EXTRA PASSED" in p.stdout, p.stdout + p.stderr
