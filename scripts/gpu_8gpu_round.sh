@@ -1,4 +1,4 @@
-# 8-GPU validation + scaling (gpurun --gpus 8 -- bash scripts/run8.sh)
+# 8-GPU validation + scaling (gpurun --gpus 8 -- bash scripts/gpu_8gpu_round.sh)
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 timeout 300 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu8.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu8.log; tail -n 3 gpurun_out/pytest_gpu8.log
