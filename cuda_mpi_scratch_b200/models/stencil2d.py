@@ -411,10 +411,8 @@ class StencilGroup:
             last = i == len(chunks) - 1
             for s in self.ranks:
                 s.step(n, residual=residual and last, drain=False)
-            if multi_dev:
-                # different devices run concurrently: keep ranks within one step
-                # of each other exactly like separate processes would be
-                pass
+        # virtual ranks on several devices run concurrently; the epoch flags keep them within one
+        # sweep of each other exactly as they keep separate processes, so no host sync per sweep
         if multi_dev:
             self.sync()
         for s in self.ranks:
