@@ -143,7 +143,7 @@ def main() -> int:
 
     tot = world.allreduce_sum(float(fails))
     if rank == 0:
-        print("COLLECTIVES_CHECK", "PASSED" if tot == 0 else f"FAILED ({int(tot)})", flush=True)
+        print("COLLECTIVES_CHECK PASSED" if tot == 0 else f"COLLECTIVES_CHECK FAILED ({int(tot)})", flush=True)
         if a.json:
             json.dump({"n_gpus": P, "iters": a.iters, "timing": "CUDA events, max over ranks, us per call",
                        "rows": rows, "check": "PASSED" if tot == 0 else "FAILED"}, open(a.json, "w"), indent=1)

@@ -139,9 +139,12 @@ class Datatype:
 
     @property
     def size(self) -> int:
-        v = _i64()
-        _lib.check(_L.b2c_type_size(self._h, C.byref(v)))
-        return v.value
+        s = getattr(self, "_size", None)     # a datatype is immutable once built
+        if s is None:
+            v = _i64()
+            _lib.check(_L.b2c_type_size(self._h, C.byref(v)))
+            s = self._size = v.value
+        return s
 
     @property
     def extent(self) -> int:

@@ -38,8 +38,10 @@ for _, r in sends:
     r.wait()
 tot = np.zeros(1, dtype=np.int32)
 world.allreduce(np.array([bad], dtype=np.int32), tot, cm.SUM)
-print(f"rank {world.rank}: {len(mine_in)} received, {len(mine_out)} sent, bad={bad}", flush=True)
+# one write() per line: several processes share the pipe, and print() writes text and newline separately
+sys.stdout.write(f"rank {world.rank}: {len(mine_in)} received, {len(mine_out)} sent, bad={bad}\n")
 if world.rank == 0:
-    print("COMM_STRESS", "PASSED" if tot[0] == 0 else f"FAILED ({int(tot[0])})", flush=True)
+    sys.stdout.write("COMM_STRESS PASSED\n" if tot[0] == 0 else f"COMM_STRESS FAILED ({int(tot[0])})\n")
+sys.stdout.flush()
 world.finalize()
 sys.exit(0 if tot[0] == 0 else 1)

@@ -88,7 +88,8 @@ def main():
     st.close()
     tot = world.allreduce_sum(float(fails))
     if world.rank == 0:
-        print("MP_STENCIL_CHECK", "PASSED" if tot == 0 else f"FAILED ({int(tot)})", flush=True)
+        sys.stdout.write("MP_STENCIL_CHECK PASSED\n" if tot == 0 else f"MP_STENCIL_CHECK FAILED ({int(tot)})\n")
+        sys.stdout.flush()
     world.finalize()
     return 0 if tot == 0 else 1
 
