@@ -32,6 +32,7 @@
 #include "b200comm.h"
 #include "b200comm/error.hpp"
 #include "core/capi_util.hpp"
+#include "core/trace.hpp"
 #include "kernels/ptx.cuh"
 
 namespace b200 {
@@ -359,6 +360,7 @@ B2C_EXPORT int b2c_coll_destroy(b2c_coll* h) { B2C_TRY delete h; B2C_CATCH }
 B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_t count, int dtype,
                                   int op, int root, int algo, int phases, void* stream) {
     B2C_TRY
+    trace::Scope ts("coll_allreduce(enqueue)", "device", -1, -3, -1, count);
     B200_REQUIRE(h && in && out && count >= 0, ERR_ARG, "bad argument");
     B200_REQUIRE(dtype == 5 || dtype == 6 || dtype == 8 || dtype == 9, ERR_TYPE,
                  "device reductions support int32, int64, float32, float64");
@@ -390,6 +392,7 @@ B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_
 B2C_EXPORT int b2c_coll_move(b2c_coll* h, int kind, const void* sendbuf, void* recvbuf,
                              size_t block_bytes, int root, int phases, void* stream) {
     B2C_TRY
+    trace::Scope ts("coll_move(enqueue)", "device", -1, -3, kind, (int64_t)block_bytes);
     B200_REQUIRE(h, ERR_ARG, "null handle");
     B200_REQUIRE(kind >= 0 && kind <= 3, ERR_ARG, "unknown collective kind");
     Plan& p = h->p;

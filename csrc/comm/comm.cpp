@@ -1,5 +1,6 @@
 // Communicators, groups, Cartesian topology, host collectives, environment.
 // See include/b200comm/comm.hpp for the reference call sites covered.
+#include "core/trace.hpp"
 #include "b200comm/comm.hpp"
 
 #include <unistd.h>
@@ -49,7 +50,10 @@ static const CommImpl& need(const std::shared_ptr<CommImpl>& p) {
 // ------------------------------------------------------------------ requests
 void Request::wait(Status* st) {
     if (!s_) return;
+    trace::Scope ts("wait", "p2p", -1, s_->kind == ReqState::RECV ? s_->src_world : s_->dest_world,
+                    s_->kind == ReqState::RECV ? s_->tag : s_->hdr.tag);
     if (!s_->done.load(std::memory_order_acquire)) s_->eng->wait(s_);
+    ts.set_bytes(s_->kind == ReqState::RECV ? s_->status.bytes : (int64_t)s_->total);
     if (st) *st = s_->status;
     const int err = s_->status.error;
     if (err) B200_FAIL(err, s_->kind == ReqState::RECV ? "receive failed" : "send failed");
@@ -102,20 +106,25 @@ int Comm::world_rank_of(int r) const {
 
 Request Comm::isend(const void* buf, int64_t count, const Datatype& t, int dest, int tag) const {
     const CommImpl& c = need(p_);
+    trace::Scope ts("isend", "p2p", c.eng->rank(), dest, tag, t.valid() ? t.size() * count : -1);
     return Request(c.eng->isend(buf, count, t, world_rank_of(dest), tag, c.ctx));
 }
 Request Comm::irecv(void* buf, int64_t count, const Datatype& t, int src, int tag) const {
     const CommImpl& c = need(p_);
+    trace::Scope ts("irecv", "p2p", c.eng->rank(), src, tag, t.valid() ? t.size() * count : -1);
     return Request(c.eng->irecv(buf, count, t, world_rank_of(src), tag, c.ctx, c.inv));
 }
 void Comm::send(const void* buf, int64_t count, const Datatype& t, int dest, int tag) const {
+    trace::Scope ts("send", "p2p", need(p_).eng->rank(), dest, tag, t.valid() ? t.size() * count : -1);
     isend(buf, count, t, dest, tag).wait();
 }
 void Comm::recv(void* buf, int64_t count, const Datatype& t, int src, int tag, Status* st) const {
+    trace::Scope ts("recv", "p2p", need(p_).eng->rank(), src, tag, t.valid() ? t.size() * count : -1);
     irecv(buf, count, t, src, tag).wait(st);
 }
 Status Comm::probe(int src, int tag) const {
     const CommImpl& c = need(p_);
+    trace::Scope ts("probe", "p2p", c.eng->rank(), src, tag);
     return c.eng->probe(world_rank_of(src), tag, c.ctx, c.inv);
 }
 bool Comm::iprobe(int src, int tag, Status* st) const {
@@ -125,6 +134,7 @@ bool Comm::iprobe(int src, int tag, Status* st) const {
 void Comm::sendrecv(const void* sbuf, int64_t scount, const Datatype& st, int dest, int stag,
                     void* rbuf, int64_t rcount, const Datatype& rt, int src, int rtag,
                     Status* status) const {
+    trace::Scope ts("sendrecv", "p2p", need(p_).eng->rank(), dest, stag, st.valid() ? st.size() * scount : -1);
     Request r = irecv(rbuf, rcount, rt, src, rtag);
     Request s = isend(sbuf, scount, st, dest, stag);
     r.wait(status);
@@ -200,6 +210,7 @@ void reduce_into(void* acc, const void* in, int64_t n, Basic k, Op op) {
 }  // namespace
 
 void Comm::barrier() const {
+    trace::Scope ts("barrier", "coll", need(p_).eng->rank());
     const CommImpl& c = need(p_);
     Coll k{c};
     const int n = size(), me = rank();
@@ -214,6 +225,7 @@ void Comm::barrier() const {
 }
 
 void Comm::bcast(void* buf, int64_t count, const Datatype& t, int root) const {
+    trace::Scope ts("bcast", "coll", need(p_).eng->rank());
     const CommImpl& c = need(p_);
     Coll k{c};
     const int n = size(), me = rank();
@@ -237,6 +249,7 @@ void Comm::bcast(void* buf, int64_t count, const Datatype& t, int root) const {
 
 void Comm::reduce(const void* sbuf, void* rbuf, int64_t count, const Datatype& t, Op op,
                   int root) const {
+    trace::Scope ts("reduce", "coll", need(p_).eng->rank());
     const CommImpl& c = need(p_);
     Coll k{c};
     const int n = size(), me = rank();
@@ -265,6 +278,7 @@ void Comm::reduce(const void* sbuf, void* rbuf, int64_t count, const Datatype& t
 }
 
 void Comm::allreduce(const void* sbuf, void* rbuf, int64_t count, const Datatype& t, Op op) const {
+    trace::Scope ts("allreduce", "coll", need(p_).eng->rank());
     std::vector<char> tmp((size_t)(t.size() * count));
     reduce(sbuf, rank() == 0 ? rbuf : tmp.data(), count, t, op, 0);
     bcast(rbuf, count, t, 0);
@@ -272,6 +286,7 @@ void Comm::allreduce(const void* sbuf, void* rbuf, int64_t count, const Datatype
 
 void Comm::gather(const void* sbuf, int64_t scount, const Datatype& st, void* rbuf,
                   int64_t rcount, const Datatype& rt, int root) const {
+    trace::Scope ts("gather", "coll", need(p_).eng->rank());
     const CommImpl& c = need(p_);
     Coll k{c};
     const int n = size(), me = rank();
@@ -297,6 +312,7 @@ void Comm::gather(const void* sbuf, int64_t scount, const Datatype& st, void* rb
 
 void Comm::scatter(const void* sbuf, int64_t scount, const Datatype& st, void* rbuf,
                    int64_t rcount, const Datatype& rt, int root) const {
+    trace::Scope ts("scatter", "coll", need(p_).eng->rank());
     const CommImpl& c = need(p_);
     Coll k{c};
     const int n = size(), me = rank();
@@ -322,6 +338,7 @@ void Comm::scatter(const void* sbuf, int64_t scount, const Datatype& st, void* r
 
 void Comm::allgather(const void* sbuf, int64_t scount, const Datatype& st, void* rbuf,
                      int64_t rcount, const Datatype& rt) const {
+    trace::Scope ts("allgather", "coll", need(p_).eng->rank());
     gather(sbuf, scount, st, rbuf, rcount, rt, 0);
     bcast(rbuf, rcount * size(), rt, 0);
 }

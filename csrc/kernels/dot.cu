@@ -30,6 +30,7 @@
 #include "b200comm.h"
 #include "b200comm/error.hpp"
 #include "core/capi_util.hpp"
+#include "core/trace.hpp"
 #include "kernels/ptx.cuh"
 
 namespace b200 {
@@ -282,6 +283,7 @@ B2C_EXPORT int b2c_dot_destroy(b2c_dot* h) {
 B2C_EXPORT int b2c_dot_run(b2c_dot* h, const void* x, const void* y, int64_t n, int dtype, int root,
                            int phases, void* stream) {
     B2C_TRY
+    trace::Scope ts("dot_run(enqueue)", "device", -1, -3, -1, n);
     B200_REQUIRE(h && (x || n == 0) && (y || n == 0), ERR_ARG, "null argument");
     B200_REQUIRE(dtype == 8 || dtype == 9, ERR_TYPE, "dot supports float32 and float64");
     B200_REQUIRE(n >= 0, ERR_COUNT, "negative length");

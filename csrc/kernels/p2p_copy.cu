@@ -22,6 +22,7 @@
 #include "b200comm.h"
 #include "b200comm/error.hpp"
 #include "core/capi_util.hpp"
+#include "core/trace.hpp"
 #include "kernels/ptx.cuh"
 
 namespace b200 {
@@ -228,6 +229,7 @@ B2C_EXPORT int b2c_p2p_put(void* dst, const void* src, size_t bytes, void* peer_
                            unsigned long long flag_value, void* counter, int mode, int max_ctas,
                            void* stream) {
     B2C_TRY
+    trace::Scope ts("p2p_put(enqueue)", "device", -1, -3, -1, (int64_t)bytes);
     B200_REQUIRE((dst && src) || bytes == 0, ERR_BUFFER, "null buffer");
     B200_REQUIRE(counter != nullptr, ERR_ARG, "null arrival counter");
     PutParams P{};

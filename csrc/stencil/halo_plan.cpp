@@ -4,6 +4,7 @@
 #include "b200comm.h"
 #include "b200comm/stencil2d.hpp"
 #include "core/capi_util.hpp"
+#include "core/trace.hpp"
 #include "core/handles.hpp"
 
 namespace b200 {
@@ -130,6 +131,7 @@ HaloPlan::HaloPlan(const comm::Comm& cart, const Array2D& tile, int stencilWidth
 }
 
 void HaloPlan::exchange(void* data) const {
+    trace::Scope ts("halo_exchange", "halo", -1, -3, -1, bytes_sent_per_exchange());
     std::vector<comm::Request> reqs;
     reqs.reserve(recv_.size() + send_.size());
     for (const TransferInfo& t : recv_) reqs.push_back(cart_.irecv(data, 1, t.type, t.peer, t.tag));

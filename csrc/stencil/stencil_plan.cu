@@ -18,6 +18,7 @@
 #include "b200comm.h"
 #include "b200comm/error.hpp"
 #include "core/capi_util.hpp"
+#include "core/trace.hpp"
 #include "stencil/stencil_kernel.cuh"
 #include "stencil/stencil_strip_kernel.cuh"
 
@@ -760,6 +761,7 @@ static int drain_impl(Plan& p, bool xchg, cudaStream_t st) {
 // complete when the stream is synchronised).
 B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* stream) {
     B2C_TRY
+    trace::Scope ts("stencil_step(enqueue)", "device", -1, -3, nsteps);
     B200_REQUIRE(h && nsteps >= 0, ERR_ARG, "bad argument");
     Plan& p = h->p;
     cudaStream_t st = (cudaStream_t)stream;
@@ -845,6 +847,7 @@ B2C_EXPORT int b2c_stencil_advance(b2c_stencil* h, long long nsteps) {
 
 B2C_EXPORT int b2c_stencil_drain(b2c_stencil* h, void* stream) {
     B2C_TRY
+    trace::Scope ts("stencil_drain(enqueue)", "device");
     B200_REQUIRE(h, ERR_ARG, "null plan");
     h->p.launches += drain_impl(h->p, false, (cudaStream_t)stream);
     B2C_CATCH
@@ -854,6 +857,7 @@ B2C_EXPORT int b2c_stencil_drain(b2c_stencil* h, void* stream) {
 // into the neighbours' ghost cells and bump their exchange counters.
 B2C_EXPORT int b2c_stencil_exchange_push(b2c_stencil* h, void* stream) {
     B2C_TRY
+    trace::Scope ts("stencil_exchange_push(enqueue)", "device");
     B200_REQUIRE(h, ERR_ARG, "null plan");
     Plan& p = h->p;
     XchgParams xp{};
@@ -877,6 +881,7 @@ B2C_EXPORT int b2c_stencil_exchange_push(b2c_stencil* h, void* stream) {
 // Phase 2: wait until every neighbour's push of the same exchange has landed.
 B2C_EXPORT int b2c_stencil_exchange_wait(b2c_stencil* h, void* stream) {
     B2C_TRY
+    trace::Scope ts("stencil_exchange_wait(enqueue)", "device");
     B200_REQUIRE(h, ERR_ARG, "null plan");
     h->p.launches += drain_impl(h->p, true, (cudaStream_t)stream);
     B2C_CATCH

@@ -27,6 +27,19 @@ const char* b2c_error_class_string(int code);
 int b2c_set_error_mode(int mode); /* 0 = return codes/exceptions, 1 = print + abort */
 int b2c_version(void);
 
+/* ---------------------------------------------------------------- tracing */
+/* Host-side spans of every communication call and every enqueue of a device operation,
+ * written as Chrome trace-event JSON.  Reference: MPI_Wtime / clock() brackets by hand
+ * (test-benchmark/mpi-pingpong-gpu.cpp:51-57, mpicuda3.cu:176-179,315-325).
+ * mode bit 0: record spans, bit 1: NVTX ranges.  Environment: B200COMM_TRACE=<prefix> records
+ * from load time and writes <prefix>.<pid>.json at exit; B200COMM_NVTX=1 emits NVTX ranges. */
+int b2c_trace_enable(int mode);
+int b2c_trace_clear(void);
+int b2c_trace_count(int64_t* n);
+int b2c_trace_dump(const char* path, int64_t* n);
+int b2c_trace_begin(const char* name, uint64_t* t0);
+int b2c_trace_end(const char* name, uint64_t t0, int rank, int64_t bytes);
+
 /* ------------------------------------------------------- device + memory */
 /* Rank -> GPU binding.  Reference: mpicuda2.cu:198-202 (task % device_count,
  * round-robin over nodes) and stencil2d/mpi-2d-stencil-subarray-cuda.cu:40-73
