@@ -123,3 +123,27 @@ def test_random_traffic_between_process_ranks(nranks, seed):
                         os.path.join(root, "tests/mp/comm_stress_proc.py"), str(seed)],
                        cwd=root, capture_output=True, text=True, timeout=240)
     assert p.returncode == 0 and "COMM_STRESS PASSED" in p.stdout, p.stdout + p.stderr
+
+
+def test_launcher_stops_the_job_when_one_rank_dies(tmp_path):
+    """Failure detection at job level: rank 1 dies while the others wait for its message; the
+    launcher terminates them and reports the failing exit code instead of hanging."""
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    prog = tmp_path / "dies.py"
+    prog.write_text(
+        "import os, sys\n"
+        f"sys.path.insert(0, {root!r})\n"
+        "import numpy as np\n"
+        "from cuda_mpi_scratch_b200.parallel import comm as cm\n"
+        "w = cm.init_process()\n"
+        "w.set_timeout(60.0)\n"
+        "if w.rank == 1:\n"
+        "    os._exit(7)\n"
+        "buf = np.zeros(4)\n"
+        "w.recv(buf, 1, 0)\n")
+    t0 = time.time()
+    p = subprocess.run([sys.executable, "-m", "cuda_mpi_scratch_b200.launch", "-n", "3", "--timeout", "90", str(prog)],
+                       cwd=root, capture_output=True, text=True, timeout=120)
+    assert p.returncode == 7
+    assert time.time() - t0 < 45, "the surviving ranks must be stopped, not left to time out"
