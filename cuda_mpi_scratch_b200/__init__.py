@@ -22,6 +22,11 @@ from .parallel.world import (LocalGroup, SingleWorld, TorchWorld, World, bind_de
                              processor_name, wtime)
 from .parallel.symmetric import SymmetricBuffer
 from .models.stencil2d import Stencil2D, StencilGroup, jacobi_coeffs, reference_step
+from .models.dot import DistributedDot
+from . import models, ops, parallel, utils                       # noqa: F401  (cms.ops.p2p, cms.utils.trace, ...)
+from .ops import collectives, p2p, pack_move                     # noqa: F401
+from .parallel import comm, datatype, halo                       # noqa: F401
+from .utils import ranks, timing, trace                          # noqa: F401
 
 __version__ = "0.1.0"
 
