@@ -355,6 +355,39 @@ inline int MPI_Allgather(const void* s, int sn, MPI_Datatype st, void* r, int rn
 inline int MPI_Type_create_hvector(int n, int bl, MPI_Aint stride, MPI_Datatype old, MPI_Datatype* out) {
     return b2c_type_hvector(n, bl, stride, old, out);
 }
+inline int MPI_Type_create_indexed_block(int n, int bl, const int* disp, MPI_Datatype old, MPI_Datatype* out) {
+    std::vector<int> bls((size_t)(n > 0 ? n : 1), bl);
+    return b2c_type_indexed(n, bls.data(), disp, old, out);
+}
+// MPI_Pack / MPI_Unpack on host buffers: the packed stream is the concatenation of the
+// typemap's bytes, `*position` advances by the packed size.
+inline int MPI_Pack_size(int count, MPI_Datatype t, MPI_Comm, int* size) {
+    int64_t s = 0;
+    int rc = b2c_type_size(t, &s);
+    *size = (int)(s * count);
+    return rc;
+}
+inline int MPI_Pack(const void* inbuf, int count, MPI_Datatype t, void* outbuf, int outsize, int* position,
+                    MPI_Comm) {
+    int64_t s = 0;
+    int rc = b2c_type_size(t, &s);
+    if (rc) return rc;
+    if (*position + s * count > outsize) return 14;   /* truncation */
+    rc = b2c_type_pack(t, inbuf, count, static_cast<char*>(outbuf) + *position);
+    if (!rc) *position += (int)(s * count);
+    return rc;
+}
+inline int MPI_Unpack(const void* inbuf, int insize, int* position, void* outbuf, int count, MPI_Datatype t,
+                      MPI_Comm) {
+    int64_t s = 0;
+    int rc = b2c_type_size(t, &s);
+    if (rc) return rc;
+    if (*position + s * count > insize) return 14;
+    rc = b2c_type_unpack(t, static_cast<const char*>(inbuf) + *position, s * count, outbuf, count);
+    if (!rc) *position += (int)(s * count);
+    return rc;
+}
+#define MPI_PACKED (b2c_shim::basic(0))
 inline int MPI_Type_create_resized(MPI_Datatype old, MPI_Aint lb, MPI_Aint extent, MPI_Datatype* out) {
     return b2c_type_resized(old, lb, extent, out);
 }

@@ -119,6 +119,29 @@ int main(int argc, char** argv) {
     MPI_Type_free(&col_r);
     MPI_Type_free(&col);
 
+    // Pack / Unpack / indexed_block: elements 1, 4, 7 of an int array travel as MPI_PACKED
+    int src9[9], dst9[9], pos = 0, psize = 0, disp3[3] = {1, 4, 7};
+    for (int i = 0; i < 9; ++i) { src9[i] = 10 * rank + i; dst9[i] = -1; }
+    MPI_Datatype pick;
+    MPI_Type_create_indexed_block(3, 1, disp3, MPI_INT, &pick);
+    MPI_Type_commit(&pick);
+    MPI_Pack_size(1, pick, MPI_COMM_WORLD, &psize);
+    CHECK(psize == 12);
+    char packed[64], inbox[64];
+    double tagalong = 0.5 + rank, tag_in = 0;
+    MPI_Pack(src9, 1, pick, packed, 64, &pos, MPI_COMM_WORLD);
+    MPI_Pack(&tagalong, 1, MPI_DOUBLE, packed, 64, &pos, MPI_COMM_WORLD);
+    CHECK(pos == 20);
+    MPI_Sendrecv(packed, pos, MPI_PACKED, right, 30, inbox, 64, MPI_PACKED, left, 30, MPI_COMM_WORLD, &st);
+    MPI_Get_count(&st, MPI_PACKED, &cnt);
+    CHECK(cnt == 20);
+    pos = 0;
+    MPI_Unpack(inbox, cnt, &pos, dst9, 1, pick, MPI_COMM_WORLD);
+    MPI_Unpack(inbox, cnt, &pos, &tag_in, 1, MPI_DOUBLE, MPI_COMM_WORLD);
+    CHECK(dst9[1] == 10 * left + 1 && dst9[4] == 10 * left + 4 && dst9[7] == 10 * left + 7 && dst9[0] == -1);
+    CHECK(tag_in == 0.5 + left && pos == 20);
+    MPI_Type_free(&pick);
+
     int total = 0, v = 0, sv = 0;
     MPI_Get_version(&v, &sv);
     CHECK(v >= 1 && MPI_Wtick() > 0);
