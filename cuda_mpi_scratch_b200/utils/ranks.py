@@ -22,9 +22,10 @@ import numpy as np
 from ..parallel import comm as cm
 
 
-def rank_print(comm, *args, file=sys.stdout, force: bool = False) -> None:
+def rank_print(comm, *args, file=None, force: bool = False) -> None:
     if os.environ.get("B2C_NO_LOG") == "1" and not force:
         return
+    file = sys.stdout if file is None else file      # resolved at call time (stdout may be redirected)
     text = f"{cm.processor_name()} - rank {comm.rank}:\t" + " ".join(str(a) for a in args) + "\n"
     file.write(text)
     file.flush()
