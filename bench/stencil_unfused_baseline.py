@@ -34,6 +34,7 @@ import torch.distributed as dist
 
 import cuda_mpi_scratch_b200 as cms
 from cuda_mpi_scratch_b200.models.stencil2d import Stencil2D, jacobi_coeffs
+from cuda_mpi_scratch_b200.ops.unfused_halo import UnfusedHalo
 
 
 def main() -> int:
@@ -64,34 +65,10 @@ def main() -> int:
     loc.fill(0.0, 0.0)
     loc.core.copy_(init)
 
-    north, south = cart.neighbour(rank, -1, 0), cart.neighbour(rank, 1, 0)
-    west, east = cart.neighbour(rank, 0, -1), cart.neighbour(rank, 0, 1)
-    send = {k: torch.empty((g, tw) if k in "ns" else (th, g), dtype=torch.float64, device=device) for k in "nswe"}
-    recv = {k: torch.empty_like(send[k]) for k in "nswe"}
-
-    pairs = [("n", north), ("s", south), ("w", west), ("e", east)]
-    opposite = {"n": "s", "s": "n", "w": "e", "e": "w"}
+    halo = UnfusedHalo(cart, rank, (th, tw), g, device)
 
     def exchange():
-        core, tile = loc.core, loc.tile           # views of the CURRENT buffer
-        send["n"].copy_(core[:g, :]); send["s"].copy_(core[-g:, :])          # pack
-        send["w"].copy_(core[:, :g]); send["e"].copy_(core[:, -g:])
-        ops = []
-        for key, peer in pairs:                   # my `key` edge fills the peer's OPPOSITE ghost
-            if peer == rank:
-                recv[opposite[key]].copy_(send[key])
-            else:
-                ops.append(dist.P2POp(dist.isend, send[key], peer))
-        # receives in the opposite order: when north and south are the same peer (2 ranks in a
-        # column) its first message to me is its north edge, which is my SOUTH ghost
-        for key, peer in (("s", south), ("n", north), ("e", east), ("w", west)):
-            if peer != rank:
-                ops.append(dist.P2POp(dist.irecv, recv[key], peer))
-        if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
-        tile[:g, g:-g].copy_(recv["n"]); tile[-g:, g:-g].copy_(recv["s"])    # unpack into the ghosts
-        tile[g:-g, :g].copy_(recv["w"]); tile[g:-g, -g:].copy_(recv["e"])
+        halo.exchange(loc.core, loc.tile)         # views of the CURRENT buffer
 
     def step(k):
         for _ in range(k):

@@ -147,3 +147,17 @@ def test_launcher_stops_the_job_when_one_rank_dies(tmp_path):
                        cwd=root, capture_output=True, text=True, timeout=120)
     assert p.returncode == 7
     assert time.time() - t0 < 45, "the surviving ranks must be stopped, not left to time out"
+
+
+@pytest.mark.parametrize("py,px", [(1, 1), (1, 2), (2, 1), (2, 2), (2, 4), (3, 1)])
+def test_unfused_baseline_halo_exchange_orderings(py, px):
+    """The baseline the fused stencil is compared against (ops/unfused_halo.py) on the CPU with
+    gloo: ghost strips hold the right neighbour's right edge on every grid shape, including the
+    ones where north == south, west == east, or a direction wraps onto the rank itself."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    port = 29710 + py * 10 + px
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={py * px}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port),
+                        os.path.join(root, "tests/mp/unfused_halo_check.py"), str(py), str(px)],
+                       cwd=root, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and "UNFUSED_HALO PASSED" in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
