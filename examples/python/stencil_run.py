@@ -7,7 +7,8 @@ import torch
 import cuda_mpi_scratch_b200 as cms
 
 world = cms.init()
-st = cms.Stencil2D.create(world, (4096, 4096), radius=1)
+temporal = int(sys.argv[1]) if len(sys.argv) > 1 else 3       # time steps per kernel sweep (1..4)
+st = cms.Stencil2D.create(world, (4096, 4096), radius=1, temporal=temporal)
 r, c = st.cart.coords(world.rank)
 st.fill(0.0, 0.0)
 if (r, c) == (0, 0):
@@ -17,5 +18,6 @@ st.exchange()
 steps, res = st.run(until=lambda x: x < 1e-3, check_every=100, max_steps=5000)
 st.check()
 if world.rank == 0:
-    print(f"{world.size} GPUs, grid {st.cart.dims}: {steps} steps, residual {res:.3e}", flush=True)
+    print(f"{world.size} GPUs, grid {st.cart.dims}, {temporal} step(s) per sweep: {steps} steps, "
+          f"residual {res:.3e}", flush=True)
 world.finalize()
