@@ -1,0 +1,233 @@
+"""Model check of the fused kernel's halo protocol (DESIGN.md "Halo protocol / hazards").
+
+compute-sanitizer is refused on this GPU pool, so the race argument of the design is checked on a
+model instead: ranks, tiles, CTAs, per-direction epoch counters and double-buffered ghost regions
+are simulated at the granularity the kernel works at (one tile = wait on flags, read ghost slices,
+push edge slices into the neighbours' ghost regions of the OTHER buffer, signal), and a random
+scheduler interleaves the CTAs of all ranks.  Every ghost slice carries the time level it holds;
+the checker asserts
+
+  RAW  a tile of step s only ever reads ghost slices that hold level s, and
+  WAR  a slice is only overwritten after every tile that had to read its previous content has
+       done so,
+
+and that no schedule deadlocks.  The same checker must FIND a violation when the protocol is
+broken in the ways the design says would be wrong (wait one epoch short, signal before the push,
+single-buffered ghosts, corners not waited for).  The reference has no race detection at all, only
+one deliberately racy kernel (ref_parallel-dot-product-atomics.cu:26-32).
+"""
+from __future__ import annotations
+
+import random
+
+import pytest
+
+DIRS = ["NW", "N", "NE", "W", "E", "SW", "S", "SE"]          # order of MPIGridCellID
+OFF = {"NW": (-1, -1), "N": (-1, 0), "NE": (-1, 1), "W": (0, -1), "E": (0, 1), "SW": (1, -1), "S": (1, 0), "SE": (1, 1)}
+OPP = {d: DIRS[7 - i] for i, d in enumerate(DIRS)}
+
+
+class Violation(Exception):
+    pass
+
+
+def decode_order(nbx, nby):
+    """Boundary ring first, interior x-fastest (decode_tile in stencil_kernel.cuh)."""
+    if nby == 1:
+        return [(x, 0) for x in range(nbx)]
+    out = [(x, 0) for x in range(nbx)] + [(x, nby - 1) for x in range(nbx)]
+    out += [(0, y) for y in range(1, nby - 1)]
+    if nbx > 1:
+        out += [(nbx - 1, y) for y in range(1, nby - 1)]
+    out += [(x, y) for y in range(1, nby - 1) for x in range(1, nbx - 1)]
+    return out
+
+
+def edge_dirs(tx, ty, nbx, nby):
+    n, s, w, e = ty == 0, ty == nby - 1, tx == 0, tx == nbx - 1
+    d = set()
+    if n: d.add("N")
+    if s: d.add("S")
+    if w: d.add("W")
+    if e: d.add("E")
+    if n and w: d.add("NW")
+    if n and e: d.add("NE")
+    if s and w: d.add("SW")
+    if s and e: d.add("SE")
+    return d
+
+
+class Rank:
+    def __init__(self, rid, nbx, nby):
+        self.id, self.nbx, self.nby = rid, nbx, nby
+        self.flags = {d: 0 for d in DIRS}
+        # ghost[buffer][(region, index)] = {"level": int, "readers": set of tiles that read this level}
+        self.ghost = [dict(), dict()]
+        for b in (0, 1):
+            for x in range(nbx):
+                self.ghost[b][("N", x)] = {"level": 0 if b == 0 else -1, "readers": set()}
+                self.ghost[b][("S", x)] = {"level": 0 if b == 0 else -1, "readers": set()}
+            for y in range(nby):
+                self.ghost[b][("W", y)] = {"level": 0 if b == 0 else -1, "readers": set()}
+                self.ghost[b][("E", y)] = {"level": 0 if b == 0 else -1, "readers": set()}
+            for c in ("NW", "NE", "SW", "SE"):
+                self.ghost[b][(c, 0)] = {"level": 0 if b == 0 else -1, "readers": set()}
+
+    def slices_read_by(self, tx, ty):
+        """Ghost slices inside the TMA box of tile (tx, ty): the box reaches one halo into the
+        x/y neighbours, so an edge tile also reads the slices next to its own."""
+        nbx, nby = self.nbx, self.nby
+        out = []
+        if ty == 0:
+            out += [("N", x) for x in (tx - 1, tx, tx + 1) if 0 <= x < nbx]
+            if tx == 0: out.append(("NW", 0))
+            if tx == nbx - 1: out.append(("NE", 0))
+        if ty == nby - 1:
+            out += [("S", x) for x in (tx - 1, tx, tx + 1) if 0 <= x < nbx]
+            if tx == 0: out.append(("SW", 0))
+            if tx == nbx - 1: out.append(("SE", 0))
+        if tx == 0:
+            out += [("W", y) for y in (ty - 1, ty, ty + 1) if 0 <= y < nby]
+        if tx == nbx - 1:
+            out += [("E", y) for y in (ty - 1, ty, ty + 1) if 0 <= y < nby]
+        return out
+
+    def required_readers(self, region, idx):
+        """Tiles whose box covers the slice (they must all have read it before it is overwritten)."""
+        return {(tx, ty) for (tx, ty) in decode_order(self.nbx, self.nby)
+                if (region, idx) in self.slices_read_by(tx, ty)}
+
+
+class Sim:
+    def __init__(self, py, px, nbx, nby, ctas, steps, rng, corners=True, bug=None):
+        self.py, self.px, self.nbx, self.nby, self.ctas, self.steps = py, px, nbx, nby, ctas, steps
+        self.rng, self.corners, self.bug = rng, corners, bug
+        self.ranks = [Rank(r, nbx, nby) for r in range(py * px)]
+        self.order = decode_order(nbx, nby)
+        # per rank: current step and the per-CTA cursor (index into its tile list, phase)
+        self.step = [0] * len(self.ranks)
+        self.cta = [self._fresh_ctas() for _ in self.ranks]
+
+    def _fresh_ctas(self):
+        lists = [self.order[c::self.ctas] for c in range(self.ctas)]
+        return [{"tiles": l, "i": 0, "phase": 0} for l in lists]
+
+    def neighbour(self, r, d):
+        y, x = divmod(r, self.px)
+        dy, dx = OFF[d]
+        return ((y + dy) % self.py) * self.px + (x + dx) % self.px      # periodic
+
+    def contrib(self, d):
+        return 1 if len(d) == 2 else (self.nbx if d in "NS" else self.nby)
+
+    def active(self, tx, ty):
+        return {d for d in edge_dirs(tx, ty, self.nbx, self.nby) if self.corners or len(d) == 1}
+
+    def runnable(self):
+        out = []
+        for r, rk in enumerate(self.ranks):
+            if self.step[r] >= self.steps:
+                continue
+            for c, st in enumerate(self.cta[r]):
+                if st["i"] >= len(st["tiles"]):
+                    continue
+                if st["phase"] == 0 and not self._flags_ready(r, st):
+                    continue
+                out.append((r, c))
+        return out
+
+    def _flags_ready(self, r, st):
+        tx, ty = st["tiles"][st["i"]]
+        s = self.step[r]
+        need = s - 1 if self.bug == "wait_one_short" else s
+        for d in self.active(tx, ty):
+            if self.bug == "skip_corner_wait" and len(d) == 2:
+                continue
+            if self.ranks[r].flags[d] < need * self.contrib(d):
+                return False
+        return True
+
+    def advance(self, r, c):
+        rk, st, s = self.ranks[r], self.cta[r][c], self.step[r]
+        tx, ty = st["tiles"][st["i"]]
+        act = self.active(tx, ty)
+        inb = 0 if self.bug == "single_buffer" else s % 2
+        outb = 0 if self.bug == "single_buffer" else (s + 1) % 2
+        phase = st["phase"]
+        if phase == 0:                       # flags acquired (checked by runnable())
+            st["phase"] = 1
+        elif phase == 1:                     # TMA load of the box: reads ghost slices of the input buffer
+            for key in rk.slices_read_by(tx, ty):
+                if not self.corners and len(key[0]) == 2:
+                    continue                 # star stencil: corner cells are loaded but never used
+                g = rk.ghost[inb][key]
+                if g["level"] != s:
+                    raise Violation(f"RAW: rank {r} step {s} tile {(tx, ty)} read {key} at level {g['level']}")
+                g["readers"].add((tx, ty))
+            st["phase"] = 2
+        elif phase in (2, 3):
+            # phase 2 = push, phase 3 = signal -- swapped in the "signal_before_push" variant
+            do_push = (phase == 2) != (self.bug == "signal_before_push")
+            if do_push:                      # my edges -> the neighbours' ghosts (other buffer)
+                for d in act:
+                    nb = self.ranks[self.neighbour(r, d)]
+                    region = OPP[d]
+                    idx = 0 if len(d) == 2 else (tx if d in "NS" else ty)
+                    g = nb.ghost[outb][(region, idx)]
+                    if g["level"] >= 0 and g["level"] != s + 1:
+                        missing = nb.required_readers(region, idx) - g["readers"]
+                        if not self.corners and len(region) == 2:
+                            missing = set()
+                        if missing:
+                            raise Violation(f"WAR: rank {r} step {s} overwrote {region, idx} of rank {nb.id} "
+                                            f"(level {g['level']}) before tiles {sorted(missing)} read it")
+                    g["level"] = s + 1
+                    g["readers"] = set()
+            else:                            # release-increment the neighbours' counters
+                self._signal(r, act)
+            if phase == 2:
+                st["phase"] = 3
+                return
+            st["phase"] = 0
+            st["i"] += 1
+            if all(x["i"] >= len(x["tiles"]) for x in self.cta[r]):      # kernel of this step finished
+                self.step[r] += 1
+                self.cta[r] = self._fresh_ctas()
+
+    def _signal(self, r, act):
+        for d in act:
+            self.ranks[self.neighbour(r, d)].flags[OPP[d]] += 1
+
+    def run(self):
+        while any(s < self.steps for s in self.step):
+            ready = self.runnable()
+            if not ready:
+                raise Violation(f"deadlock at steps {self.step}")
+            self.advance(*self.rng.choice(ready))
+        # skew between ranks never exceeded one step by construction of the waits; final state:
+        for rk in self.ranks:
+            for d in DIRS:
+                assert rk.flags[d] == self.steps * self.contrib(d) * (1 if (self.corners or len(d) == 1) else 0)
+
+
+GRIDS = [(1, 1, 3, 2), (1, 2, 3, 3), (2, 2, 2, 2), (2, 3, 4, 1), (3, 3, 1, 1), (2, 1, 5, 3)]
+
+
+@pytest.mark.parametrize("py,px,nbx,nby", GRIDS)
+@pytest.mark.parametrize("corners", [True, False])
+def test_protocol_is_hazard_free_under_random_schedules(py, px, nbx, nby, corners):
+    for seed in range(40):
+        rng = random.Random(seed * 7919 + py * 100 + px * 10 + nbx)
+        Sim(py, px, nbx, nby, ctas=rng.choice([1, 2, 3, 5]), steps=5, rng=rng, corners=corners).run()
+
+
+@pytest.mark.parametrize("bug", ["wait_one_short", "signal_before_push", "single_buffer", "skip_corner_wait"])
+def test_checker_finds_the_hazard_when_the_protocol_is_broken(bug):
+    found = 0
+    for seed in range(200):
+        rng = random.Random(seed)
+        try:
+            Sim(2, 2, 3, 3, ctas=3, steps=4, rng=rng, corners=True, bug=bug).run()
+        except Violation:
+            found += 1
+    assert found > 0, f"the model checker missed the '{bug}' hazard in 200 random schedules"
