@@ -231,3 +231,61 @@ def test_checker_finds_the_hazard_when_the_protocol_is_broken(bug):
         except Violation:
             found += 1
     assert found > 0, f"the model checker missed the '{bug}' hazard in 200 random schedules"
+
+
+# ------------------------------------------------------------------------------------------------
+# Fused dot + allreduce: {value, epoch} slots, two parities.
+class DotSim:
+    """Each rank, per epoch e: write {e} into slot[e % parities][me] of EVERY rank, then wait until all
+    P slots of that parity in its OWN table carry epoch e, then read them one by one.  A rank starts
+    epoch e+1 only when its epoch-e kernel has finished (stream order)."""
+
+    def __init__(self, nranks, epochs, rng, parities=2):
+        self.P, self.E, self.rng, self.par = nranks, epochs, rng, parities
+        self.table = [[[0] * nranks for _ in range(parities)] for _ in range(nranks)]   # [rank][parity][src] = epoch
+        self.state = [{"e": 1, "phase": "write", "k": 0} for _ in range(nranks)]
+
+    def run(self):
+        while any(s["e"] <= self.E for s in self.state):
+            ready = []
+            for r, s in enumerate(self.state):
+                if s["e"] > self.E:
+                    continue
+                if s["phase"] == "wait" and any(v < s["e"] for v in self.table[r][s["e"] % self.par]):
+                    continue
+                ready.append(r)
+            if not ready:
+                raise Violation("dot: deadlock")
+            r = self.rng.choice(ready)
+            s = self.state[r]
+            e, p = s["e"], s["e"] % self.par
+            if s["phase"] == "write":                  # one peer store per scheduling step
+                self.table[s["k"]][p][r] = e
+                s["k"] += 1
+                if s["k"] == self.P:
+                    s["phase"], s["k"] = "wait", 0
+            elif s["phase"] == "wait":
+                s["phase"] = "read"
+            else:                                       # read slot k of my table
+                if self.table[r][p][s["k"]] != e:
+                    raise Violation(f"dot: rank {r} epoch {e} read slot {s['k']} holding epoch "
+                                    f"{self.table[r][p][s['k']]}")
+                s["k"] += 1
+                if s["k"] == self.P:
+                    s["e"], s["phase"], s["k"] = e + 1, "write", 0
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 8])
+def test_dot_slot_protocol_two_parities_are_enough(nranks):
+    for seed in range(100):
+        DotSim(nranks, epochs=6, rng=random.Random(seed)).run()
+
+
+def test_dot_slot_protocol_one_parity_is_not_enough():
+    found = 0
+    for seed in range(200):
+        try:
+            DotSim(3, epochs=6, rng=random.Random(seed), parities=1).run()
+        except Violation:
+            found += 1
+    assert found > 0
