@@ -4,26 +4,45 @@
 Metric (BASELINE.json): 2D-stencil Gcell-updates/s at 1/2/4/8 B200, device
 timed, max over ranks.  Weak scaling: every GPU owns a 16384^2 tile of a
 periodic Py x Px Cartesian grid (1x1, 1x2, 2x2, 2x4); one step = one Jacobi
-sweep of every tile INCLUDING the halo exchange, which is fused into the same
+time step of every tile INCLUDING the halo exchange, which is fused into the same
 kernel (peer stores over NVLink + device-side epoch flags).  By default the kernel is the
 temporally blocked one (``--temporal 3``): every sweep over the grid advances THREE time steps
 (ghost width 3, corners exchanged), bit-identical to three single steps, so the grid is read
-and written once per three updates; the JSON also carries the ``--temporal 1`` number.
+and written once per three updates.
 
     python bench.py --gpus 1 --steps 20 --warmup 3
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
         --master-addr 127.0.0.1 --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 3
 
-Rank 0 prints ONE JSON line.  ``--impl reference`` is the reference arm: the
-reference cannot be installed or built on this image (no setup.py/pyproject,
-and no MPI library or compiler wrapper anywhere), so it reports
-``unavailable``; see DESIGN.md "Reference arm".
+Four arms run in the same process, on the same grid, for the same K time steps per timed
+batch, all timed on the device (CUDA events bracketed by barrier + synchronize, max over ranks):
+
+  1. ``value``                  fused stencil+halo kernel, T time steps per sweep (the product);
+  2. ``one_time_step_per_sweep`` the same fused kernel with one exchange per time step (T = 1);
+  3. ``unfused_baseline``       what the reference's loop does on this box
+                                 (``stencil2d/mpi-2d-stencil-subarray-cuda.cu:169-172``:
+                                 ``do { ExchangeData; Compute } while(...)`` with
+                                 ``stencil2d/stencil2D.h:363-377``: all receives, all sends, one
+                                 wait): pack -> NCCL ``batch_isend_irecv`` -> unpack -> this
+                                 repo's stencil kernel on a plan WITHOUT neighbours, per time step;
+  4. ``e2e``                    arm 1 through the public API with per-sweep pinned H2D of the
+                                 coefficients and D2H + host read of the residual.
+
+Every arm's K-step batch is repeated until ``--min-seconds`` of device time has passed; the
+number reported is the MEDIAN batch (min / max alongside).  After the timed regions all three
+implementations restart from the same field, run K steps, and their cores must be bit-identical
+(``verified``).  ``vs_baseline`` = arm 1 / arm 3: the reference itself cannot be built here (no
+MPI on the image, DESIGN.md "Reference arm"), so the host-driven equivalent measured in the same
+run is the comparator.
+
+Rank 0 prints ONE JSON line.  ``--impl reference`` reports ``unavailable`` (see above).
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import statistics
 import sys
 import time
 
@@ -44,6 +63,10 @@ def parse_args(argv=None):
                          "1 = one step per sweep, 0 = 3 where possible")
     ap.add_argument("--th", type=int, default=0, help="explicit per-GPU tile height (experiments)")
     ap.add_argument("--tw", type=int, default=0, help="explicit per-GPU tile width (experiments)")
+    ap.add_argument("--min-seconds", type=float, default=2.0,
+                    help="repeat the K-step batch of the headline arm until this much device time "
+                         "has passed (the other arms get half of it)")
+    ap.add_argument("--no-baseline", action="store_true", help="skip arms 2 and 3 (experiments)")
     return ap.parse_args(argv)
 
 
@@ -59,6 +82,11 @@ def reference_arm(args) -> int:
     return 0
 
 
+def _stats(ms_list, steps):
+    per = sorted(m / steps for m in ms_list)
+    return {"median": statistics.median(per), "min": per[0], "max": per[-1], "batches": len(per)}
+
+
 def main(argv=None) -> int:
     args = parse_args(argv)
     if args.impl == "reference":
@@ -67,6 +95,7 @@ def main(argv=None) -> int:
     import torch
     import cuda_mpi_scratch_b200 as cms
     from cuda_mpi_scratch_b200.models.stencil2d import Stencil2D, jacobi_coeffs
+    from cuda_mpi_scratch_b200.ops.unfused_halo import UnfusedHalo
     from cuda_mpi_scratch_b200.utils.timing import ClockSampler
 
     if not torch.cuda.is_available():
@@ -86,108 +115,165 @@ def main(argv=None) -> int:
         th, tw = args.th, args.tw
     R = args.radius
     T = args.temporal or (3 if R == 1 else 1)
+    K, Wm = args.steps, max(args.warmup, 3)
     coeffs = jacobi_coeffs(R)
+    dev = world.device
+    device = f"cuda:{dev}"
+    stream = torch.cuda.current_stream(dev)
+    cart = cms.CartTopology.create(dims, True)
+    cr, cc = cart.coords(world.rank)
 
-    def make_plan(temporal):
-        # synthetic data: smooth deterministic field generated per tile on the device
-        # (state, like weights: it stays resident; per-step INPUTS are the coefficients)
-        p = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True,
-                             temporal=temporal)
-        r, c = p.cart.coords(world.rank)
-        ys = torch.arange(th, device=f"cuda:{p.device}", dtype=torch.float64) + r * th
-        xs = torch.arange(tw, device=f"cuda:{p.device}", dtype=torch.float64) + c * tw
+    # synthetic data: smooth deterministic field generated per tile on the device (state, like
+    # weights: it stays resident; the per-step INPUTS of the e2e arm are the coefficients)
+    ys = torch.arange(th, device=device, dtype=torch.float64) + cr * th
+    xs = torch.arange(tw, device=device, dtype=torch.float64) + cc * tw
+
+    def init_field(p, collective=True):
         p.fill(0.0, 0.0)
         p.core.copy_(torch.sin(ys * 1e-3)[:, None] * torch.cos(xs * 2e-3)[None, :])
         p.set_coeffs(coeffs)
-        torch.cuda.synchronize(p.device)
-        p.exchange()
-        torch.cuda.synchronize(p.device)
-        world.barrier()
+        torch.cuda.synchronize(dev)
+        if collective:
+            p.exchange()
+            torch.cuda.synchronize(dev)
+            world.barrier()
+
+    def make_plan(temporal):
+        p = Stencil2D.create(world, (th, tw), radius=R, kind="star", dims=dims, periods=True,
+                             temporal=temporal)
+        init_field(p)
         return p
 
-    st = make_plan(T)
-    dev = st.device
+    def timed_batches(run_batch, min_s, max_batches=2000, wall=False):
+        """K-step batches, each bracketed by barrier + synchronize on both sides and timed with
+        CUDA events on the launching stream (``wall``: host clock instead, for the e2e arm);
+        repeated until ``min_s`` of timed work; per-batch MAX over ranks."""
+        def one():
+            world.barrier()
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record(stream)
+            run_batch()
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            t1 = time.perf_counter()
+            return (t1 - t0) * 1e3 if wall else e0.elapsed_time(e1)
+        first = world.allreduce_max(one())
+        reps = int(min(max_batches, max(3, -(-min_s * 1e3 // max(first, 1e-3)))))
+        local = [one() for _ in range(reps)]
+        world.barrier()
+        return world.allreduce_max_vec(local)
 
-    stream = torch.cuda.current_stream(dev)
-    # ---------------- device-timed: K fused steps ----------------
-    # clocks are sampled from before the warm-up to the end of the e2e loop so
-    # that several samples fall under load even when K steps take a few ms
-    sampler = ClockSampler(dev, period_ms=20).start() if world.rank == 0 else None
+    # ---------------- arm 1: fused, T time steps per sweep, device timed ----------------
+    st = make_plan(T)
+    sampler = ClockSampler(dev).start() if world.rank == 0 else None
     if sampler is not None:
         sampler.wait_first(2.0)
-    st.step(max(args.warmup, 3))
+    st.step(Wm)
+    st.step(K)                                   # one untimed batch of the timed shape
     torch.cuda.synchronize(dev)
-    world.barrier()
     launches0 = st.kernel_launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    st.step(K)
+    launches = st.kernel_launches - launches0    # kernels of ONE K-step batch
     torch.cuda.synchronize(dev)
-    world.barrier()
     if sampler is not None:
         sampler.window_begin()
-    e0.record(stream)
-    st.step(args.steps)
-    e1.record(stream)
-    torch.cuda.synchronize(dev)
+    ms_main = timed_batches(lambda: st.step(K), args.min_seconds)
     if sampler is not None:
         sampler.window_end()
-    world.barrier()
-    ms = e0.elapsed_time(e1)
-    launches = st.kernel_launches - launches0
-    ms_max = world.allreduce_max(ms)
     st.check()
+    main_stats = _stats(ms_main, K)
 
-    # ---------------- end to end through the public API ----------------
-    # every step: H2D of that step's coefficients from pinned memory, one fused
-    # step with residual, D2H of the residual, host reads it.
+    # ---------------- arm 4: end to end through the public API ----------------
+    # every sweep: H2D of that sweep's coefficients from pinned memory, one fused sweep with
+    # residual, D2H of the residual into pinned memory, and the host READS it -- one sweep
+    # late, so that the next sweep is already queued while the copy of this one completes
+    # (two pinned slots per direction inside Stencil2D).
     coef_host = torch.tensor(coeffs, dtype=torch.float64).pin_memory()
-    h2d = coef_host.numel() * 8
-    d2h = 8
-    for _ in range(max(1, args.warmup)):
-        st.set_coeffs(coef_host)
-        st.step(T, residual=True)
-        st.local_residual_async()
-        stream.synchronize()
-    world.barrier()
-    torch.cuda.synchronize(dev)
+    h2d, d2h = coef_host.numel() * 8, 8
+    chunks = [T] * (K // T) + ([K % T] if K % T else [])
+    evs = [torch.cuda.Event(), torch.cuda.Event()]
+    last_res = [0.0]
+
+    def e2e_batch():
+        pend = None
+        for i, nsub in enumerate(chunks):        # exactly K time steps, one sweep per iteration
+            s = i & 1
+            st.set_coeffs(coef_host)
+            st.step(nsub, residual=True)
+            buf = st.local_residual_async(s)
+            evs[s].record(stream)
+            if pend is not None:
+                evs[pend[0]].synchronize()
+                last_res[0] = float(pend[1].item())
+            pend = (s, buf)
+        evs[pend[0]].synchronize()
+        last_res[0] = float(pend[1].item())
+
+    for _ in range(2):
+        e2e_batch()
     if sampler is not None:
         sampler.window_begin()
-    t0 = time.perf_counter()
-    res = 0.0
-    chunks = [T] * (args.steps // T) + ([args.steps % T] if args.steps % T else [])
-    for nsub in chunks:                       # exactly K time steps, one kernel sweep per iteration
-        st.set_coeffs(coef_host)
-        st.step(nsub, residual=True)
-        buf = st.local_residual_async()
-        stream.synchronize()
-        res = float(buf.item())
-    torch.cuda.synchronize(dev)
-    e2e_s = time.perf_counter() - t0
+    ms_e2e = timed_batches(e2e_batch, args.min_seconds / 2, wall=True)
     if sampler is not None:
         sampler.window_end()
-    e2e_s = world.allreduce_max(e2e_s)
     clocks = sampler.stop() if sampler is not None else None
     st.check()
+    e2e_stats = _stats(ms_e2e, K)
 
-    # transparency: the same K steps with ONE time step per kernel sweep (no temporal blocking)
-    single = None
-    if T > 1:
-        st.close()
+    # ---------------- arm 2: fused, one time step per sweep ----------------
+    single_stats = st1 = None
+    if T > 1 and not args.no_baseline:
         st1 = make_plan(1)
-        st1.step(max(args.warmup, 3))
+        st1.step(Wm)
         torch.cuda.synchronize(dev)
-        world.barrier()
-        e0.record(stream)
-        st1.step(args.steps)
-        e1.record(stream)
-        torch.cuda.synchronize(dev)
-        ms1 = world.allreduce_max(e0.elapsed_time(e1))
+        single_stats = _stats(timed_batches(lambda: st1.step(K), args.min_seconds / 2), K)
         st1.check()
-        single = ms1
-        st1.close()
+
+    # ---------------- arm 3: UNFUSED baseline (pack, NCCL send/recv, unpack, separate kernel) ---
+    unf_stats = loc = None
+    if R == 1 and not args.no_baseline:
+        grp = Stencil2D.create_group(cms.LocalGroup(1, devices=[dev]), (th, tw), 1, "star",
+                                     dims=(1, 1), periods=False)
+        loc = grp.ranks[0]                        # a plan whose 8 neighbours are absent never
+        init_field(loc, collective=False)         # pushes, waits or signals inside the kernel
+        halo = UnfusedHalo(cart, world.rank, (th, tw), 1, device)
+
+        def unfused_steps(k=K):
+            for _ in range(k):
+                halo.exchange(loc.core, loc.tile)     # views of the CURRENT buffer
+                loc.step(1, drain=False)
+
+        unfused_steps(Wm)
+        torch.cuda.synchronize(dev)
+        unf_stats = _stats(timed_batches(unfused_steps, args.min_seconds / 2), K)
+        loc.check()
+
+    # ---------------- verification (outside every timed region) ----------------
+    # all implementations restart from the same field and advance K time steps: the cores must
+    # agree BIT FOR BIT (temporal blocking vs single steps vs host-driven exchange)
+    verified = None
+    if not args.no_baseline and (st1 is not None or loc is not None):
+        init_field(st)
+        st.step(K)
+        torch.cuda.synchronize(dev)
+        bad = 0.0
+        if st1 is not None:
+            init_field(st1)
+            st1.step(K)
+            torch.cuda.synchronize(dev)
+            bad += 0.0 if torch.equal(st.core, st1.core) else 1.0
+        if loc is not None:
+            init_field(loc, collective=False)
+            unfused_steps(K)
+            torch.cuda.synchronize(dev)
+            bad += 0.0 if torch.equal(st.core, loc.core) else 1.0
+        verified = world.allreduce_sum(bad) == 0.0
 
     cells = float(th) * float(tw) * n
-    value = cells * args.steps / (ms_max * 1e-3) / 1e9
-    e2e_value = cells * args.steps / e2e_s / 1e9
+    rate = lambda ms_per_step: cells / (ms_per_step * 1e-3) / 1e9
+    value = rate(main_stats["median"])
     if world.rank == 0:
         bytes_per_cell = 16.0 / T   # one read + one write of the grid per sweep of T updates
         peaks = {}
@@ -198,13 +284,37 @@ def main(argv=None) -> int:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
         per_gpu = value / n
+        nsweeps = len(chunks)
+
+        def arm(stats, what):
+            return None if stats is None else {
+                "value": round(rate(stats["median"]), 3), "unit": "Gcell/s",
+                "ms_per_step": round(stats["median"], 5),
+                "ms_per_step_min": round(stats["min"], 5), "ms_per_step_max": round(stats["max"], 5),
+                "batches": stats["batches"], "what": what}
+
+        unf = arm(unf_stats, "UNFUSED baseline, same grid and K: per time step pack (torch copies) -> "
+                             "NCCL batch_isend_irecv of the 4 edges -> unpack -> this repo's stencil "
+                             "kernel on a plan without neighbours; device timed, median batch")
+        one = arm(single_stats, "fused kernel, one time step (one halo exchange) per sweep "
+                                "(--temporal 1); device timed, median batch")
         out = {
             "metric": "2D-stencil Gcell-updates/s (5-point fp64, fused halo exchange)",
-            "value": round(value, 3), "unit": "Gcell/s", "n_gpus": n, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 5),
-            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+            "value": round(value, 3), "unit": "Gcell/s", "n_gpus": n, "steps": K,
+            "warmup": args.warmup, "ms_per_step": round(main_stats["median"], 5),
+            "ms_per_step_min": round(main_stats["min"], 5),
+            "ms_per_step_max": round(main_stats["max"], 5),
+            "timed_batches": main_stats["batches"],
+            "timed_region_s": round(sum(ms_main) * 1e-3, 3),
+            "higher_is_better": True, "scaling": args.scaling,
+            "vs_baseline": None if unf is None else round(value / unf["value"], 3),
+            "vs_baseline_what": "value / unfused_baseline.value, both measured in this run (the "
+                                "reference publishes no number and cannot be built here)",
             "dtype": "fp64", "data": "synthetic",
             "impl": "ours",
+            "verified": verified,
+            "verified_what": f"after K={K} steps from the same field the cores of the fused T={T} run, "
+                             "the fused T=1 run and the unfused baseline are bit-identical on every rank",
             "config": {"model": f"stencil2d star radius {R} ({4 * R + 1}-point) Jacobi, periodic"
                                 + (f", {T} time steps per kernel sweep (temporal blocking, bit-identical "
                                    "to single steps)" if T > 1 else ""),
@@ -214,30 +324,41 @@ def main(argv=None) -> int:
                        "l2": "inputs larger than L2 (2 x %.2f GiB per GPU vs 126 MB)"
                              % (th * tw * 8 / 2 ** 30),
                        "halo": "fused: peer stores + epoch flags inside the stencil kernel",
-                       "time_steps_per_kernel_sweep": T},
+                       "time_steps_per_kernel_sweep": T,
+                       "timing": "K-step batches, each between barrier+synchronize, CUDA events, max "
+                                 "over ranks per batch, repeated for >= %.1f s; value = median batch"
+                                 % args.min_seconds},
             "roofline": {"hbm_gbs_measured": hbm,
                          "achieved_gbs_per_gpu": round(per_gpu * bytes_per_cell, 1),
                          "fraction_of_measured_hbm": round(per_gpu * bytes_per_cell / hbm, 4)},
             "clocks": clocks,
-            "e2e": {"value": round(e2e_value, 3), "unit": "Gcell/s",
-                    "h2d_bytes_per_step": round(h2d * len(chunks) / args.steps, 3),
-                    "d2h_bytes_per_step": round(d2h * len(chunks) / args.steps, 3),
+            "unfused_baseline": unf,
+            "one_time_step_per_sweep": one,
+            "fused_vs_unfused_one_step_per_sweep":
+                None if (unf is None or one is None) else round(one["value"] / unf["value"], 3),
+            "e2e": {"value": round(rate(e2e_stats["median"]), 3), "unit": "Gcell/s",
+                    "ms_per_step": round(e2e_stats["median"], 5),
+                    "ms_per_step_min": round(e2e_stats["min"], 5),
+                    "ms_per_step_max": round(e2e_stats["max"], 5), "batches": e2e_stats["batches"],
+                    "h2d_bytes_per_step": round(h2d * nsweeps / K, 3),
+                    "d2h_bytes_per_step": round(d2h * nsweeps / K, 3),
+                    "vs_unfused_baseline": None if unf is None else
+                        round(rate(e2e_stats["median"]) / unf["value"], 3),
                     "what": f"Stencil2D.set_coeffs(pinned) + step({T}, residual=True) + residual "
-                            "D2H + host read, every kernel sweep; wall clock, max over ranks",
-                    "last_residual_sumsq": res},
-            "one_time_step_per_sweep": None if single is None else {
-                "value": round(cells * args.steps / (single * 1e-3) / 1e9, 3), "unit": "Gcell/s",
-                "ms_per_step": round(single / args.steps, 5),
-                "what": "same grid and K steps without temporal blocking (--temporal 1), device timed"},
+                            "D2H into pinned memory + host read (one sweep late, next sweep already "
+                            "queued), every kernel sweep; wall clock per K-step batch, max over "
+                            "ranks, median batch",
+                    "last_residual_sumsq": last_res[0]},
             "gpu_launches": launches,
-            "launches_note": "counted by the native plan: 1 fused stencil+halo kernel per sweep "
-                             f"({T} time step(s) each), then 1 step-counter bump, 1 flag drain and "
-                             "1 ghost-column unpack per batch",
+            "launches_note": "kernels of ONE timed K-step batch, counted by the native plan: 1 fused "
+                             f"stencil+halo kernel per sweep ({T} time step(s) each), then 1 "
+                             "step-counter bump, 1 flag drain and 1 ghost-column unpack per batch",
         }
         print(json.dumps(out))
     world.barrier()
-    if single is None:
-        st.close()
+    for p in (st, st1, loc):
+        if p is not None:
+            p.close()
     world.finalize()
     return 0
 

@@ -209,6 +209,7 @@ struct Plan {
     int tilesX, tilesY;
     int tile_h;                  // output rows per kernel tile (kTileH; 64 for 3-4 levels per sweep)
     int partial_levels;          // kind 2: levels of the NEXT sweep if fewer than R (0 = all)
+    int debug;                   // B2C_STENCIL_DEBUG, read ONCE when the plan is created
     uint64_t contrib[8];         // signals per step a neighbour sends me per direction
     unsigned long long launches; // kernels launched through this plan (for bench accounting)
     // ---- strip kernel (algo 1) ----
@@ -553,6 +554,7 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
     p.tilesX = (W + kTileW - 1) / kTileW;
     p.tilesY = (H + p.tile_h - 1) / p.tile_h;
     p.timeout_ns = 20ull * 1000 * 1000 * 1000;
+    { const char* dbg = std::getenv("B2C_STENCIL_DEBUG"); p.debug = dbg ? std::atoi(dbg) : 0; }
 
     // shared memory / grid
     const int RA = (R + 1) & ~1;
@@ -798,7 +800,7 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         lp.my_land[1] = reinterpret_cast<const double*>(p.base + p.L.off_land[in][1]);
         lp.W = p.L.W; lp.H = p.L.H; lp.g = p.L.g; lp.lead = p.L.lead; lp.pitch = p.L.pitch;
         lp.tilesX = p.tilesX; lp.tilesY = p.tilesY; lp.push_corners = p.push_corners;
-        { const char* dbg = std::getenv("B2C_STENCIL_DEBUG"); lp.debug = dbg ? std::atoi(dbg) : 0; }
+        lp.debug = p.debug;
         const bool resid = (flags & 1) && s == nsteps - 1;
         launch_step(p, lp, resid, st);
         p.launches += resid ? 2 : 1;

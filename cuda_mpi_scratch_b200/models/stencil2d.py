@@ -86,10 +86,13 @@ class Stencil2D:
                                                    C.c_void_p(symbuf.local_ptr), C.byref(nbr),
                                                    int(push_corners)))
         self._h = h
-        self._coef_pinned = torch.empty(128, dtype=torch.float64).pin_memory() \
-            if torch.cuda.is_available() else torch.empty(128, dtype=torch.float64)
-        self._resid_pinned = torch.zeros(1, dtype=torch.float64).pin_memory() \
-            if torch.cuda.is_available() else torch.zeros(1, dtype=torch.float64)
+        # Host staging comes in PAIRS (coefficients in, residual out) so that a caller can keep
+        # one sweep in flight while it reads the result of the previous one: slot i of sweep i,
+        # slot i^1 still owned by the copy of sweep i-1 (see bench.py's end-to-end loop).
+        pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
+        self._coef_pinned = pin(torch.empty(2, 128, dtype=torch.float64))
+        self._resid_pinned = pin(torch.zeros(2, dtype=torch.float64))
+        self._coef_slot = 0
         self._graph_launches = 0
         self._time_steps = 0
 
@@ -178,10 +181,14 @@ class Stencil2D:
                     _lib.check(_lib.lib.b2c_stencil_fill(self._h, b, 1, float(core_value), st))
 
     def set_coeffs(self, coeffs: Sequence[float]) -> None:
-        """Copy stencil coefficients host(pinned) -> device on the current stream."""
+        """Copy stencil coefficients host(pinned) -> device on the current stream.  The pinned
+        staging area alternates between two slots, so a second call may follow before the copy
+        of the first has run (not a third: synchronise at least every other call)."""
         n = len(coeffs)
-        self._coef_pinned[:n] = torch.as_tensor(coeffs, dtype=torch.float64)
-        ptr = C.cast(self._coef_pinned.data_ptr(), C.POINTER(C.c_double))
+        stage = self._coef_pinned[self._coef_slot]
+        self._coef_slot ^= 1
+        stage[:n] = torch.as_tensor(coeffs, dtype=torch.float64)
+        ptr = C.cast(stage.data_ptr(), C.POINTER(C.c_double))
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_set_coef(self._h, ptr, n, _stream_ptr(self.device)))
 
@@ -262,15 +269,17 @@ class Stencil2D:
         self._time_steps -= nsteps
         return StencilGraph(self, g, nsteps, per_replay)
 
-    def local_residual_async(self) -> torch.Tensor:
-        """Start the D2H copy of the last step's local sum of squared updates into
-        pinned memory; valid after the stream is synchronised."""
+    def local_residual_async(self, slot: int = 0) -> torch.Tensor:
+        """Start the D2H copy of the last step's local sum of squared updates into pinned memory
+        (``slot`` 0 or 1); the returned 1-element tensor is valid once the stream (or an event
+        recorded after this call) has been synchronised."""
         inf = self.info()
+        dst = self._resid_pinned[slot:slot + 1]
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib.b2c_memcpy_async(C.c_void_p(self._resid_pinned.data_ptr()),
+            _lib.check(_lib.lib.b2c_memcpy_async(C.c_void_p(dst.data_ptr()),
                                                  C.c_void_p(inf.resid), 8, 2,
                                                  _stream_ptr(self.device)))
-        return self._resid_pinned
+        return dst
 
     def check(self) -> None:
         """Synchronise and raise if a device-side wait timed out."""

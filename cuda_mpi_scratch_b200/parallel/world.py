@@ -80,6 +80,10 @@ class World:
     def allreduce_sum(self, x: float) -> float:
         raise NotImplementedError
 
+    def allreduce_max_vec(self, xs: Sequence[float]) -> list[float]:
+        """Element-wise max over ranks of a list of numbers (per-batch timings)."""
+        return [self.allreduce_max(float(x)) for x in xs]
+
     def abort(self, code: int = 1) -> None:
         """``MPI_Abort`` (``mpierr.h:41``)."""
         os._exit(code)
@@ -155,6 +159,12 @@ class TorchWorld(World):
 
     def allreduce_sum(self, x):
         return self._allreduce(x, self._dist.ReduceOp.SUM)
+
+    def allreduce_max_vec(self, xs):
+        t = self._torch.tensor([float(x) for x in xs], dtype=self._torch.float64)
+        if t.numel():
+            self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX, group=self._cpu_group)
+        return t.tolist()
 
     def finalize(self):
         if self._owns_pg and self._dist.is_initialized():
