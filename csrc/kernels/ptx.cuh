@@ -113,6 +113,12 @@ __device__ __forceinline__ void fence_proxy_async() {
     asm volatile("fence.proxy.async;" ::: "memory");
 }
 
+// Same, restricted to shared memory: orders this thread's generic st.shared against later bulk
+// copies that read or overwrite the same bytes, WITHOUT waiting for outstanding global stores.
+__device__ __forceinline__ void fence_proxy_async_smem() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
 // ---- cross-GPU flags (system scope) ---------------------------------------------
 __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* p) {
     uint64_t v;
@@ -133,6 +139,11 @@ __device__ __forceinline__ void st_relaxed_sys(uint64_t* p, uint64_t v) {
 // Release-increment of a counter that may live on a peer GPU.
 __device__ __forceinline__ void red_add_release_sys(uint64_t* p, uint64_t v) {
     asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Relaxed increment: pair it with ONE fence_acq_rel_sys() before a batch of signals instead of a
+// release (= a full system-scope barrier) per signal.
+__device__ __forceinline__ void red_add_relaxed_sys(uint64_t* p, uint64_t v) {
+    asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void fence_acq_rel_sys() {
     asm volatile("fence.acq_rel.sys;" ::: "memory");
@@ -158,6 +169,17 @@ __device__ __forceinline__ void st_v4(void* p, const int4& v) {
 }
 __device__ __forceinline__ void st_cs_v2f64(double* p, double a, double b) {
     asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(a), "d"(b) : "memory");
+}
+
+// Register re-partitioning between the warpgroups of a warp-specialised CTA (all warps of a
+// warpgroup execute it; counts are multiples of 8).
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
 }
 
 // Named barrier among a subset of the CTA's threads (id 1..15; 0 is __syncthreads).

@@ -21,6 +21,7 @@
 #include "core/trace.hpp"
 #include "stencil/stencil_kernel.cuh"
 #include "stencil/stencil_strip_kernel.cuh"
+#include "stencil/stencil_tstrip_kernel.cuh"
 
 #include <algorithm>
 #include <vector>
@@ -220,7 +221,14 @@ struct Plan {
     int strip_grid, strip_slots;
     int strip_w;                 // cells per strip of this plan (even, <= kStripW)
     size_t strip_smem;
+    // ---- temporal strip kernel (algo 2, kind 2 only): shares d_segs / d_seg_begin ----
+    int ts_grid, ts_slots, ts_strip_w;
+    size_t ts_smem;
 };
+
+// Geometry of the temporal strip kernel: 6 columns per thread, 8 consumer warps.
+constexpr int kTsCpt = 6, kTsWarps = 8;
+using TsG = TsGeo<kTsCpt, kTsWarps>;
 
 // Strip width such that (interior strips) x (row bands) uses as many of the G CTAs as
 // possible: every CTA then owns one long segment and all CTAs of a band advance together.
@@ -253,9 +261,10 @@ constexpr int kStripSlots = 5;   // default ring depth (B2C_STRIP_SLOTS = 3..6 |
 // (pieces of the west/east strips, single top/bottom chunks of the interior strips),
 // then one contiguous run of interior chunks.  Also counts, per direction, how many
 // segments signal it -- the neighbour (same geometry) sends me exactly as many.
-static void build_strip_partition(Plan& p, int G, std::vector<Segment>& segs, std::vector<int>& begin) {
+static void build_strip_partition(Plan& p, int strip_w, int G, bool force_run,
+                                  std::vector<Segment>& segs, std::vector<int>& begin) {
     const int W = p.L.W, H = p.L.H;
-    const int NS = (W + p.strip_w - 1) / p.strip_w, CY = (H + kChunkH - 1) / kChunkH;
+    const int NS = (W + strip_w - 1) / strip_w, CY = (H + kChunkH - 1) / kChunkH;
     std::vector<std::vector<Segment>> per((size_t)G);
     std::vector<long> load((size_t)G, 0);
     auto act = [&](int d) {
@@ -303,7 +312,7 @@ static void build_strip_partition(Plan& p, int G, std::vector<Segment>& segs, st
     const char* pe = std::getenv("B2C_STRIP_PART");
     const int NSi = NS - 2, CYi = CY - 2;
     const int NB = NSi > 0 ? G / NSi : 0;        // row bands so that bands x strips <= CTAs
-    if (ich > 0 && NB >= 1 && CYi >= 8 * NB && !(pe && std::string(pe) == "run")) {
+    if (ich > 0 && NB >= 1 && CYi >= 8 * NB && !force_run && !(pe && std::string(pe) == "run")) {
         // band-major: CTA (band b, strip s) marches down rows of band b of strip s.  CTAs of
         // one band sit on ADJACENT strips and advance in lock-step, so at any instant DRAM
         // sees whole contiguous rows (like the x-fastest tile order), not scattered pieces.
@@ -451,7 +460,41 @@ static void launch_tb(const Plan& pl, const LaunchParams& lp, bool resid, cudaSt
     }
 }
 
+// kind 2, algo 2: the temporal strip kernel; LV < T is the partial sweep
+template <int T, int LV>
+static void launch_ts_lv(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    TsParams sp{};
+    sp.lp = lp;
+    sp.segs = pl.d_segs;
+    sp.seg_begin = pl.d_seg_begin;
+    sp.strip_w = pl.ts_strip_w;
+    sp.nslots = pl.ts_slots;
+    sp.resid = resid ? 1 : 0;
+    auto k = stencil_tstrip_kernel<T, LV, kTsCpt, kTsWarps>;
+    static bool attr_done[64] = {};
+    if (!attr_done[pl.device & 63]) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)ts_smem_bytes<T, kTsCpt, kTsWarps>(3)));
+        attr_done[pl.device & 63] = true;
+    }
+    k<<<pl.ts_grid, TsG::THREADS, pl.ts_smem, st>>>(sp);
+    B200_CHECK_LAUNCH();
+}
+
+template <int T>
+static void launch_ts(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    const int lv = (pl.partial_levels > 0 && pl.partial_levels < T) ? pl.partial_levels : T;
+    if constexpr (T >= 3) if (lv == 2) { launch_ts_lv<T, 2>(pl, lp, resid, st); return; }
+    if (lv == 1) { launch_ts_lv<T, 1>(pl, lp, resid, st); return; }
+    launch_ts_lv<T, T>(pl, lp, resid, st);
+}
+
 static void launch_step(const Plan& pl, const LaunchParams& lp, bool resid, cudaStream_t st) {
+    if (pl.kind == 2 && pl.algo == 2) {
+        if (pl.L.R == 2) launch_ts<2>(pl, lp, resid, st);
+        else launch_ts<3>(pl, lp, resid, st);
+        return;
+    }
     if (pl.kind == 2) {
         switch (pl.L.R) {
             case 2: launch_tb<2>(pl, lp, resid, st); return;
@@ -645,7 +688,7 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         p.strip_smem = (size_t)p.strip_slots * kChunkBytes + 128 + 2 * p.strip_slots * sizeof(uint64_t);
         std::vector<Segment> segs;
         std::vector<int> begin;
-        build_strip_partition(p, p.strip_grid, segs, begin);
+        build_strip_partition(p, p.strip_w, p.strip_grid, false, segs, begin);
         B200_CHECK_CUDA(cudaMalloc(&p.d_segs, std::max<size_t>(1, segs.size()) * sizeof(Segment)));
         B200_CHECK_CUDA(cudaMalloc(&p.d_seg_begin, begin.size() * sizeof(int)));
         B200_CHECK_CUDA(cudaMemcpy(p.d_segs, segs.data(), segs.size() * sizeof(Segment), cudaMemcpyHostToDevice));
@@ -663,10 +706,52 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
                          "cuTensorMapEncodeTiled (strip) failed with CUresult " + std::to_string((int)r));
         }
     }
+    // ---- temporal strip kernel (kind 2): strips of <= 1536 columns marched top to bottom, the
+    // time levels in registers (stencil_tstrip_kernel.cuh).  Default whenever the tile gives every
+    // CTA a long enough march; B2C_TB_ALGO=strip|tile overrides.
+    if (kind == 2) {
+        const char* ae = std::getenv("B2C_TB_ALGO");
+        const int NS = (W + TsG::SWMAX - 1) / TsG::SWMAX;
+        int sw = (((W + NS - 1) / NS) + kTsCpt - 1) / kTsCpt * kTsCpt;
+        if (const char* we = std::getenv("B2C_TS_WIDTH")) {
+            const int v = std::atoi(we) / kTsCpt * kTsCpt;
+            if (v >= kTsCpt && v <= TsG::SWMAX) sw = v;
+        }
+        const int NS2 = (W + sw - 1) / sw;
+        const int last = W - (NS2 - 1) * sw;
+        const int CY = (H + kChunkH - 1) / kChunkH;
+        const bool eligible = R <= 3 && H >= 16 && last >= R && (H % kChunkH == 0 || H % kChunkH >= R);
+        const long steps_per_cta = (long)NS2 * CY / std::max(1, prop.multiProcessorCount);
+        bool use = eligible && steps_per_cta >= 48;
+        if (ae && std::string(ae) == "strip") {
+            B200_REQUIRE(eligible, ERR_ARG, "temporal strip kernel not applicable to this tile");
+            use = true;
+        }
+        if (ae && std::string(ae) == "tile") use = false;
+        if (use) {
+            p.algo = 2;
+            p.ts_strip_w = sw;
+            p.ts_grid = (int)std::max<long>(1, std::min<long>(prop.multiProcessorCount, (long)NS2 * CY / 4));
+            p.ts_slots = 3;
+            if (const char* se = std::getenv("B2C_TS_SLOTS")) {
+                const int v = std::atoi(se);
+                if (v >= 2 && v <= 3) p.ts_slots = v;
+            }
+            p.ts_smem = R == 2 ? ts_smem_bytes<2, kTsCpt, kTsWarps>(p.ts_slots)
+                               : ts_smem_bytes<3, kTsCpt, kTsWarps>(p.ts_slots);
+            std::vector<Segment> segs;
+            std::vector<int> begin;
+            build_strip_partition(p, sw, p.ts_grid, true, segs, begin);
+            B200_CHECK_CUDA(cudaMalloc(&p.d_segs, std::max<size_t>(1, segs.size()) * sizeof(Segment)));
+            B200_CHECK_CUDA(cudaMalloc(&p.d_seg_begin, begin.size() * sizeof(int)));
+            B200_CHECK_CUDA(cudaMemcpy(p.d_segs, segs.data(), segs.size() * sizeof(Segment), cudaMemcpyHostToDevice));
+            B200_CHECK_CUDA(cudaMemcpy(p.d_seg_begin, begin.data(), begin.size() * sizeof(int), cudaMemcpyHostToDevice));
+        }
+    }
     p.ncoef = kind == 2 ? 5 : (kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1));
     B200_CHECK_CUDA(cudaMalloc(&p.coef_dev, 128 * sizeof(double)));
     B200_CHECK_CUDA(cudaMalloc(&p.resid_partials,
-                               (size_t)std::max(p.grid, p.strip_grid) * sizeof(double)));
+                               (size_t)std::max(std::max(p.grid, p.strip_grid), p.ts_grid) * sizeof(double)));
     // default: Jacobi average of the 4R (or (2R+1)^2-1) neighbours
     double hc[128] = {0};
     const int nn = p.ncoef - 1;
@@ -710,10 +795,10 @@ B2C_EXPORT int b2c_stencil_info(b2c_stencil* h, b2c_stencil_info_t* o) {
     B200_REQUIRE(h && o, ERR_ARG, "null argument");
     const Plan& p = h->p;
     o->cur = p.cur; o->steps_done = p.steps_done;
-    o->grid = p.algo == 1 ? p.strip_grid : p.grid;
-    o->threads = p.algo == 1 ? kStripThreads : kThreads;
-    o->smem_bytes = p.algo == 1 ? p.strip_smem : p.smem;
-    o->nstages = p.algo == 1 ? p.strip_slots : p.nstages; o->tiles_x = p.tilesX; o->tiles_y = p.tilesY;
+    o->grid = p.algo == 2 ? p.ts_grid : (p.algo == 1 ? p.strip_grid : p.grid);
+    o->threads = p.algo == 2 ? TsG::THREADS : (p.algo == 1 ? kStripThreads : kThreads);
+    o->smem_bytes = p.algo == 2 ? p.ts_smem : (p.algo == 1 ? p.strip_smem : p.smem);
+    o->nstages = p.algo == 2 ? p.ts_slots : (p.algo == 1 ? p.strip_slots : p.nstages); o->tiles_x = p.tilesX; o->tiles_y = p.tilesY;
     o->ncoef = p.ncoef; o->launches_per_step = 1;
     o->buf[0] = p.base + p.L.off_x[0]; o->buf[1] = p.base + p.L.off_x[1];
     o->resid = reinterpret_cast<double*>(p.base + kOffResid);
@@ -805,7 +890,8 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         launch_step(p, lp, resid, st);
         p.launches += resid ? 2 : 1;
         if (resid) {
-            sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials, p.algo == 1 ? p.strip_grid : p.grid,
+            sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials,
+                                                   p.algo == 2 ? p.ts_grid : (p.algo == 1 ? p.strip_grid : p.grid),
                                                    reinterpret_cast<double*>(p.base + kOffResid));
             B200_CHECK_LAUNCH();
         }

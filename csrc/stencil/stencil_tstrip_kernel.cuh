@@ -1,0 +1,416 @@
+// Temporally blocked stencil + halo kernel, third generation: column STRIPS marched from top to
+// bottom with the time levels carried in REGISTERS (radius-1 star, T = 2..4 time steps per sweep).
+//
+// Why (ncu + bench of the tile kernel with 3 levels per sweep, profiles/README.md): every thread
+// of the tile kernel owns 2 columns x 16 rows of a 128 x 64 tile and recomputes the intermediate
+// levels of its whole neighbourhood: 7.0 cell updates per output cell instead of 3.  That made the
+// kernel FP64/LDS bound (0.69 of its HBM roofline) and, sustained, POWER bound (1000 W cap,
+// clocks down to 1845 MHz).  Here
+//   * a CTA owns a strip of up to NWARPS*32*CPT columns and marches down it; every input row is
+//     loaded ONCE (one 1-D bulk copy per row into a ring of 4-row chunks);
+//   * a thread owns CPT (6) adjacent columns and keeps, for every time level k < LV, the three
+//     newest rows of a window that is (LV-k) columns wider on either side.  Each new input row
+//     yields one row of every level; the output row lags LV rows behind the input row.  Nothing
+//     intermediate touches shared or global memory, no barrier separates the levels, and there is
+//     NO vertical redundancy: (10+8+6)/6 = 4.0 cell updates per output cell for 3 levels;
+//   * 6 columns = 48 bytes per lane makes the 16-byte shared-memory loads of a quarter warp hit
+//     eight different bank groups (3*lane mod 8 is a permutation): no bank conflicts without any
+//     swizzle (4 columns per lane would be 2-way conflicted).
+// The halo protocol is the one of the other two kernels (per-direction epoch counters, acquire
+// before a boundary segment is loaded, ghost columns patched from the landing buffers, release
+// after the pushes), and so is the work partition of the strip kernel: every CTA does its boundary
+// segments FIRST, then a balanced run of interior chunks.  Edge rows and edge columns are staged in
+// shared memory and leave as full 128-byte lines (rows) / contiguous bursts (columns).
+// Bit-identical to T single steps: every value is formed with the operation order of the
+// single-step kernel.
+//
+// Reference counterpart: none -- the reference's Compute() is an empty stub
+// (stencil2d/mpi-2d-stencil-subarray-cuda.cu:32-33) and its exchange is host-driven
+// (stencil2d/stencil2D.h:363-377).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <type_traits>
+
+#include "kernels/ptx.cuh"
+#include "stencil/stencil_kernel.cuh"
+#include "stencil/stencil_strip_kernel.cuh"   // Segment
+
+namespace b200 {
+namespace stencil {
+
+constexpr int kTsChunkH = 4;         // rows per ring slot == granularity of the segments
+constexpr int kTsRA = 4;             // halo columns loaded on either side (keeps 16-byte alignment)
+constexpr int kTsColStageRows = 32;  // edge-column rows staged before one burst
+static_assert(kTsChunkH == kChunkH, "the strip partition builder is shared");
+
+template <int CPT, int NWARPS>
+struct TsGeo {
+    static constexpr int CONS = NWARPS * 32;             // consumer threads
+    // + a producer WARPGROUP (only its first lane works).  Registers are handed out per SM
+    // sub-partition, so a 9th warp would cap every thread at 168 registers; with a whole extra
+    // warpgroup the producer side shrinks to 40 registers (setmaxnreg.dec) and the consumers grow
+    // to 232 (setmaxnreg.inc) -- the windows of three time levels need ~200.
+    static constexpr int THREADS = CONS + 128;
+    static constexpr int PRODUCER_REGS = 40, CONSUMER_REGS = 232;
+    static constexpr int SWMAX = CONS * CPT;             // widest strip (cells)
+    static constexpr int PITCH = SWMAX + 2 * kTsRA;      // shared-memory row pitch (elements)
+    static constexpr int SLOT_BYTES = PITCH * kTsChunkH * 8;
+    static_assert(SLOT_BYTES % 128 == 0, "slot alignment");
+};
+
+struct TsParams {
+    LaunchParams lp;          // same fields as the tile kernel (tilesX/tilesY unused)
+    const Segment* segs;      // all segments, grouped per CTA
+    const int* seg_begin;     // [gridDim.x + 1] offsets into segs
+    int strip_w;              // cells per strip (a multiple of CPT, <= SWMAX)
+    int nslots;               // ring depth
+    int resid;                // accumulate the residual of the last level
+};
+
+// Dynamic shared memory: nslots ring slots, then the output stage (per warp 2 halves x 2 rows of
+// 32*CPT cells), then 2*nslots mbarriers.
+template <int T, int CPT, int NWARPS>
+constexpr size_t ts_smem_bytes(int nslots) {
+    return (size_t)nslots * TsGeo<CPT, NWARPS>::SLOT_BYTES + (size_t)4 * TsGeo<CPT, NWARPS>::SWMAX * 8 +
+           2 * (size_t)nslots * sizeof(uint64_t);
+}
+
+// T: ghost width of the plan (= levels of a full sweep); LV: levels computed by THIS sweep
+// (LV < T: the partial sweep that ends a run whose step count is not a multiple of T).
+template <int T, int LV, int CPT, int NWARPS>
+__global__ void __launch_bounds__(TsGeo<CPT, NWARPS>::THREADS, 1)
+stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
+    using G = TsGeo<CPT, NWARPS>;
+    constexpr int CH = kTsChunkH, RA = kTsRA;
+    static_assert(T >= 2 && T <= 4 && LV >= 1 && LV <= T, "levels");
+    static_assert(CPT % 2 == 0 && CPT >= T && RA >= T, "columns per thread");
+    const LaunchParams& P = SP.lp;
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int nslots = SP.nslots;
+    double* ostage = reinterpret_cast<double*>(smem + (size_t)nslots * G::SLOT_BYTES);
+    uint64_t* full = reinterpret_cast<uint64_t*>(ostage + 4 * G::SWMAX);
+    uint64_t* empty = full + nslots;
+    __shared__ double red_smem[NWARPS];
+    __shared__ double colstage[2][kTsColStageRows][T];   // [west|east][row][k]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int sbeg = SP.seg_begin[blockIdx.x], send = SP.seg_begin[blockIdx.x + 1];
+
+    if (tid == 0) {
+        for (int s = 0; s < nslots; ++s) {
+            ptx::mbar_init(&full[s], 1);
+            ptx::mbar_init(&empty[s], NWARPS);
+        }
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp >= NWARPS) {
+        // ===================== producer: flag acquire + one bulk copy per row =====================
+        ptx::setmaxnreg_dec<G::PRODUCER_REGS>();
+        if (warp == NWARPS && lane == 0) {
+            int slot = 0;
+            uint32_t phase = 0;
+            const int rows_total = P.H + 2 * P.g;
+            for (int s = sbeg; s < send; ++s) {
+                const Segment sg = SP.segs[s];
+                const unsigned act = sg.dirs;
+                if (act && !(P.debug & 2)) {
+                    const uint64_t t0 = ptx::globaltimer_ns();
+                    for (int d = 0; d < 8; ++d) {
+                        if (!(act >> d & 1u)) continue;
+                        uint32_t spins = 0;
+                        const uint64_t need = (*P.step_ctr + P.step_off) * P.signals_per_step[d];
+                        while (ptx::ld_acquire_sys(P.my_flags + d) < need) {
+                            if ((++spins & 1023u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
+                                atomicOr(P.status, 1u);
+                                break;
+                            }
+                        }
+                    }
+                    // ghost rows were written by another GPU's generic proxy; the bulk copies
+                    // below read them through the async proxy
+                    ptx::fence_proxy_async();
+                }
+                const int x0 = sg.strip * SP.strip_w;
+                const int sw = min(SP.strip_w, P.W - x0);
+                const uint32_t row_bytes = (uint32_t)(sw + 2 * RA) * 8u;
+                const double* col0 = P.in + P.lead + x0 - RA;
+                for (int j = sg.j0 - 1; j <= sg.j1; ++j) {
+                    ptx::mbar_wait(&empty[slot], phase ^ 1u);
+                    // rows of the chunk that exist in the padded buffer (the chunk above the
+                    // first and below the last core chunk stick out by 4 - T rows)
+                    const int pr0 = P.g + j * CH;
+                    const int ra = max(0, -pr0), rb = min(CH, rows_total - pr0);
+                    const int nrows = max(0, rb - ra);
+                    ptx::mbar_arrive_expect_tx(&full[slot], (uint32_t)nrows * row_bytes);
+                    unsigned char* dst = smem + (size_t)slot * G::SLOT_BYTES;
+                    for (int r = ra; r < rb; ++r)
+                        ptx::bulk_load_1d(dst + (size_t)r * G::PITCH * 8,
+                                          col0 + (size_t)(pr0 + r) * P.pitch, row_bytes, &full[slot]);
+                    if (++slot == nslots) { slot = 0; phase ^= 1u; }
+                }
+            }
+        }
+        return;
+    }
+
+    // =============================== consumers ===============================
+    ptx::setmaxnreg_inc<G::CONSUMER_REGS>();
+    constexpr int W0 = CPT + 2 * RA;    // level-0 window: columns c0-RA .. c0+CPT+RA-1
+    double c[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) c[k] = __ldg(P.coef + k);
+    const int c0 = CPT * tid;           // my first column inside the strip
+    double racc = 0.0;
+    int slot = 0;                       // mirrors the producer's ring position
+    uint32_t phase = 0;
+    // lv[k][row % 3][col]: the three newest rows of time level k.  Level k covers columns
+    // c0-(LV-k) .. c0+CPT-1+(LV-k) (level 0: the aligned window above).  All indices are
+    // compile-time constants after unrolling, so the windows live in registers.
+    double lv[LV][3][W0];
+#pragma unroll
+    for (int k = 0; k < LV; ++k)
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int b = 0; b < W0; ++b) lv[k][a][b] = 0.0;
+
+    for (int s = sbeg; s < send; ++s) {
+        const Segment sg = SP.segs[s];
+        const unsigned act = sg.dirs;
+        const int x0 = sg.strip * SP.strip_w;
+        const int sw = min(SP.strip_w, P.W - x0);              // valid columns of this strip (even)
+        const bool west = x0 == 0, east = x0 + sw == P.W;
+        const bool patch = (act & kColDirs) != 0;
+        const int ylo = sg.j0 * CH, yhi = min(sg.j1 * CH, P.H);  // output rows of this segment
+        int staged0 = -1;                                      // first core row held in colstage
+
+        // Ghost columns of a freshly loaded chunk come from the landing buffers.
+        auto patch_chunk = [&](int jj) {
+            double* ch = reinterpret_cast<double*>(smem + (size_t)slot * G::SLOT_BYTES);
+            bool wrote = false;
+            for (int e = tid; e < 2 * CH * T; e += G::CONS) {
+                const int side = e / (CH * T), rem = e % (CH * T);
+                const int r = rem / T, q = rem % T;
+                if ((side == 0 && !west) || (side == 1 && !east)) continue;
+                const int pr = P.g + jj * CH + r;               // padded row
+                if (pr < 0 || pr >= P.H + 2 * T) continue;
+                const int vd = pr < T ? (side ? NE : NW) : (pr >= P.H + T ? (side ? SE : SW)
+                                                                          : (side ? E_ : W_));
+                if (!(act >> vd & 1u)) continue;
+                const int col = side ? RA + sw + q : RA - T + q;
+                ch[r * G::PITCH + col] = P.my_land[side][land_index(pr, T, T) + q];
+                wrote = true;
+            }
+            // generic smem writes vs the next bulk copy into this slot (writers only: the fence
+            // is slow and the other ~230 threads have nothing to order)
+            if (wrote) ptx::fence_proxy_async_smem();
+            ptx::named_bar_sync(3, G::CONS);
+        };
+        // Burst the staged edge columns [staged0, upto) into the neighbours' landing buffers.
+        auto flush_cols = [&](int upto) {
+            if (staged0 < 0 || upto <= staged0) return;
+            ptx::named_bar_sync(4, G::CONS);
+            if (warp == 0 && !(P.debug & 1)) {
+                for (int d = 0; d < 8; ++d) {
+                    const int dy = dir_dy(d), dx = dir_dx(d);
+                    if (dx == 0 || !(act >> d & 1u)) continue;
+                    if ((dx < 0 && !west) || (dx > 0 && !east)) continue;
+                    int ya = staged0, yb = upto;                  // core rows
+                    if (dy < 0) yb = min(yb, P.g);
+                    if (dy > 0) ya = max(ya, P.H - P.g);
+                    const int n = (yb - ya) * T;
+                    if (n <= 0) continue;
+                    double* dst = P.peer_land[d] + land_index(ya + P.g - dy * P.H, T, T);
+                    const double* src = &colstage[dx < 0 ? 0 : 1][ya - staged0][0];
+                    for (int e = lane; e < n; e += 32) dst[e] = src[e];
+                }
+            }
+            ptx::named_bar_sync(4, G::CONS);
+            staged0 = -1;
+        };
+        // One input row: load it, advance every level by one row, emit output row y.
+        // PH = (input row) mod 3 selects the register set of every window (compile time).  ACT:
+        // the segment touches the tile edge (staging code present); RS: residual wanted.
+        auto row = [&](auto phc, auto actc, auto rsc, const double* srow, double* orow_s, int y) {
+            constexpr int PH = decltype(phc)::value;
+            constexpr bool ACT = decltype(actc)::value, RS = decltype(rsc)::value;
+#pragma unroll
+            for (int m = 0; m < W0 / 2; ++m) {
+                const double2 v = *reinterpret_cast<const double2*>(srow + 2 * m);
+                lv[0][PH][2 * m] = v.x;
+                lv[0][PH][2 * m + 1] = v.y;
+            }
+            double outv[CPT];
+            double ctr[CPT];
+#pragma unroll
+            for (int k = 1; k <= LV; ++k) {
+                // level k-1 rows i-k-1 (north), i-k (centre), i-k+1 (south) -> level k row i-k
+                const int sN = (PH + 30 - (k + 1)) % 3, sM = (PH + 30 - k) % 3, sS = (PH + 30 - (k - 1)) % 3;
+                // column q of level k is c0-(LV-k)+q; in level k-1 its west neighbour has index
+                // q+off, itself q+off+1, its east neighbour q+off+2
+                const int off = (k == 1) ? RA - LV : 0;
+                const int ncol = CPT + 2 * (LV - k);
+#pragma unroll
+                for (int q = 0; q < ncol; ++q) {
+                    double a = c[0] * lv[k - 1][sM][q + off + 1];
+                    a = fma(c[1], lv[k - 1][sM][q + off], a);          // west
+                    a = fma(c[2], lv[k - 1][sM][q + off + 2], a);      // east
+                    a = fma(c[3], lv[k - 1][sN][q + off + 1], a);      // north
+                    a = fma(c[4], lv[k - 1][sS][q + off + 1], a);      // south
+                    if (k < LV) {
+                        lv[k < LV ? k : 0][sM][q] = a;
+                    } else {
+                        outv[q < CPT ? q : 0] = a;
+                        if (RS) ctr[q < CPT ? q : 0] = lv[k - 1][sM][q + off + 1];
+                    }
+                }
+            }
+            if (y < ylo || y >= yhi) return;              // warm-up / look-ahead rows (CTA-uniform)
+            // The output row goes to this warp's stage in shared memory (48 bytes per lane: no
+            // bank conflicts) and leaves as ONE bulk copy per warp row, issued by lane 0 (see
+            // step()).  Plain STG.128 here made the next row's arithmetic wait for the stores to
+            // read their registers (ncu: long-scoreboard stalls on the first DMUL after each STG).
+#pragma unroll
+            for (int p = 0; p < CPT / 2; ++p)
+                *reinterpret_cast<double2*>(orow_s + 2 * p) = make_double2(outv[2 * p], outv[2 * p + 1]);
+            if (RS) {
+#pragma unroll
+                for (int q = 0; q < CPT; ++q)
+                    if (c0 + q < sw) {
+                        const double d0 = outv[q] - ctr[q];
+                        racc = fma(d0, d0, racc);
+                    }
+            }
+            if (ACT) {
+                if (patch) {
+                    const int sr = y - staged0;
+#pragma unroll
+                    for (int q = 0; q < CPT; ++q) {
+                        const int xx = c0 + q;
+                        if (west && xx < T) colstage[0][sr][xx] = outv[q];
+                        if (east && xx >= sw - T && xx < sw) colstage[1][sr][xx - (sw - T)] = outv[q];
+                    }
+                }
+            }
+        };
+
+        // The march: input rows (j0-1)*4 .. (j1+1)*4-1, three per loop trip (the period of the
+        // 3-row windows, so every register index is a compile-time constant and the loop body
+        // stays small enough for the instruction cache); ring slots are taken and handed back
+        // every fourth row.
+        const int i_begin = (sg.j0 - 1) * CH, i_end = (sg.j1 + 1) * CH;
+        const double* base = nullptr;
+        // this warp's piece of an output row: columns [wcol0, wcol0 + wcells) of the strip
+        const int wcol0 = warp * 32 * CPT;
+        const int wcells = max(0, min(32 * CPT, sw - wcol0));
+        double* const ost_w = ostage + (size_t)warp * 4 * 32 * CPT;      // [half][row][32*CPT]
+        auto step = [&](auto phc, auto actc, auto rsc, int i) {
+            constexpr bool ACT = decltype(actc)::value;
+            const int r = (i - i_begin) & (CH - 1);
+            if (r == 0) {
+                ptx::mbar_wait(&full[slot], phase);
+                if (ACT) {
+                    const int jj = sg.j0 - 1 + ((i - i_begin) >> 2);
+                    if (patch) patch_chunk(jj);
+                    if (patch && staged0 < 0 && i - LV + CH > ylo) staged0 = max(i - LV, ylo);
+                }
+                base = reinterpret_cast<const double*>(smem + (size_t)slot * G::SLOT_BYTES) + c0;
+            }
+            if ((r & 1) == 0) {
+                // the half of the output stage used two bulk groups ago has been read out
+                if (lane == 0) ptx::bulk_wait_read<1>();
+                __syncwarp();
+            }
+            row(phc, actc, rsc, base + r * G::PITCH, ost_w + r * (32 * CPT) + lane * CPT, i - LV);
+            if (r & 1) {
+                // two staged rows -> global memory (and, for edge rows, the neighbour's ghost rows)
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    if (wcells > 0) {
+#pragma unroll
+                        for (int b = 1; b >= 0; --b) {
+                            const int y = i - b - LV;
+                            if (y < ylo || y >= yhi) continue;
+                            const double* src = ost_w + (r - b) * (32 * CPT);
+                            const size_t col = (size_t)P.lead + x0 + wcol0;
+                            ptx::bulk_store_1d(P.out + (size_t)(y + P.g) * P.pitch + col, src, wcells * 8);
+                            if (ACT) {
+                                if ((act >> N & 1u) && y < T)
+                                    ptx::bulk_store_1d(P.peer_out[N] + (size_t)(y + P.g + P.H) * P.pitch + col,
+                                                       src, wcells * 8);
+                                if ((act >> S & 1u) && y >= P.H - T)
+                                    ptx::bulk_store_1d(P.peer_out[S] + (size_t)(y + P.g - P.H) * P.pitch + col,
+                                                       src, wcells * 8);
+                            }
+                        }
+                    }
+                    ptx::bulk_commit();
+                }
+            }
+            if (r == CH - 1) {
+                // all shared-memory reads of this slot are done: hand it back to the producer
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&empty[slot]);
+                if (++slot == nslots) { slot = 0; phase ^= 1u; }
+                if (ACT) {
+                    const int yend = min(i - LV + 1, yhi);
+                    if (patch && staged0 >= 0 &&
+                        (yend - staged0 + CH > kTsColStageRows || i + 1 == i_end))
+                        flush_cols(yend);
+                }
+            }
+        };
+        auto march = [&](auto actc, auto rsc) {
+            for (int i = i_begin; i < i_end; i += 3) {
+                step(std::integral_constant<int, 0>{}, actc, rsc, i);
+                if (i + 1 >= i_end) break;
+                step(std::integral_constant<int, 1>{}, actc, rsc, i + 1);
+                if (i + 2 >= i_end) break;
+                step(std::integral_constant<int, 2>{}, actc, rsc, i + 2);
+            }
+        };
+        if (act) {
+            if (SP.resid) march(std::true_type{}, std::true_type{});
+            else march(std::true_type{}, std::false_type{});
+        } else {
+            if (SP.resid) march(std::false_type{}, std::true_type{});
+            else march(std::false_type{}, std::false_type{});
+        }
+
+        if (act) {
+            // my bulk copies into the neighbours' ghost rows have completed ...
+            if (lane == 0) ptx::bulk_wait<0>();
+            // ... and every consumer's peer stores happen-before thread 0's release
+            ptx::named_bar_sync(1, G::CONS);
+            if (tid == 0) {
+                ptx::fence_acq_rel_sys();
+                for (int d = 0; d < 8; ++d)
+                    if (act >> d & 1u) ptx::red_add_relaxed_sys(P.peer_flag[d], 1ull);
+            }
+        }
+    }
+
+    if (lane == 0) ptx::bulk_wait<0>();      // the output stage must outlive its last bulk copies
+    if (SP.resid) {
+        // deterministic per-CTA partial: lanes -> warps -> thread 0
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) racc += __shfl_xor_sync(0xffffffffu, racc, o);
+        if (lane == 0) red_smem[warp] = racc;
+        ptx::named_bar_sync(2, G::CONS);
+        if (tid == 0) {
+            double t = 0.0;
+#pragma unroll
+            for (int w = 0; w < NWARPS; ++w) t += red_smem[w];
+            P.resid_partials[blockIdx.x] = t;
+        }
+    }
+}
+
+}  // namespace stencil
+}  // namespace b200

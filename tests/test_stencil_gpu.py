@@ -185,6 +185,63 @@ def test_temporal_blocking_any_step_count(T):
     assert grp.residual() == pytest.approx(one.residual(), rel=1e-12)
 
 
+@pytest.mark.parametrize("T", [2, 3])
+@pytest.mark.parametrize("dims,tile_hw", [((1, 1), (96, 384)), ((2, 2), (64, 256)), ((2, 4), (40, 504)),
+                                          ((3, 3), (32, 260)), ((1, 2), (50, 200)), ((1, 1), (64, 3200)),
+                                          ((2, 2), (36, 1600)), ((1, 1), (600, 1536))])
+def test_temporal_strip_kernel_is_bit_identical_to_single_steps(monkeypatch, dims, tile_hw, T):
+    """The temporal STRIP kernel (levels in registers, strips marched top to bottom; the default
+    for large tiles) forced on small multi-rank cases: one strip, several strips with a partial
+    last one, partial last chunk, every direction a self- or aliased neighbour.  Same bits as
+    the single-step kernel and as the temporal TILE kernel, a partial sweep at the end."""
+    if tile_hw[0] % 4 and tile_hw[0] % 4 < T:
+        pytest.skip("the south edge would straddle two 4-row chunks: the plan keeps the tile kernel")
+    steps = 4 * T + (T - 1)
+    coeffs = [0.1, 0.2, 0.25, 0.15, 0.3]
+    monkeypatch.setenv("B2C_TB_ALGO", "strip")
+    tb, glob = _run_group(dims, tile_hw, 1, "star", steps, coeffs, temporal=T)
+    assert tb.ranks[0].info().threads == 384          # the strip kernel really ran
+    monkeypatch.setenv("B2C_TB_ALGO", "tile")
+    tile, _ = _run_group(dims, tile_hw, 1, "star", steps, coeffs, temporal=T)
+    assert tile.ranks[0].info().threads == 288
+    one, _ = _run_group(dims, tile_hw, 1, "star", steps, coeffs)
+    got = tb.gather_global()
+    assert torch.equal(got, one.gather_global())
+    assert torch.equal(got, tile.gather_global())
+    exp = glob.clone()
+    for _ in range(steps):
+        exp = reference_step(exp, coeffs, 1)
+    assert torch.allclose(got, exp, rtol=1e-12, atol=1e-13)
+    assert tb.residual() == pytest.approx(one.residual(), rel=1e-12)
+    s = tb.ranks[0]
+    ri = (torch.arange(-T, tile_hw[0] + T)) % exp.shape[0]
+    ci = (torch.arange(-T, tile_hw[1] + T)) % exp.shape[1]
+    assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
+
+
+@pytest.mark.parametrize("T", [2, 3])
+def test_temporal_strip_kernel_graph_replay_and_odd_step_counts(monkeypatch, T):
+    monkeypatch.setenv("B2C_TB_ALGO", "strip")
+    hw = (96, 1900)
+    plain, glob = _run_group((1, 1), hw, 1, "star", 7 * T + 2)
+    grp = Stencil2D.create_group(cms.LocalGroup(1), hw, 1, "star", dims=(1, 1), temporal=T)
+    s = grp.ranks[0]
+    s.fill(0.0, 0.0)
+    grp.scatter_global(glob)
+    grp.exchange()
+    s.step(T)
+    torch.cuda.synchronize()
+    graph = s.capture(2 * T)
+    for _ in range(3):
+        graph.replay()
+    s.step(1)
+    s.step(1)
+    torch.cuda.synchronize()
+    s.check()
+    assert s.steps_done == 7 * T + 2
+    assert torch.equal(grp.gather_global(), plain.gather_global())
+
+
 def test_temporal_blocking_rejects_what_it_cannot_do():
     with pytest.raises(ValueError):
         Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 2, "star", dims=(1, 1), temporal=2)
