@@ -474,7 +474,7 @@ static void launch_ts_lv(const Plan& pl, const LaunchParams& lp, bool resid, cud
     static bool attr_done[64] = {};
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)ts_smem_bytes<T, kTsCpt, kTsWarps>(3)));
+                                             (int)ts_smem_bytes<T, kTsCpt, kTsWarps>(6)));
         attr_done[pl.device & 63] = true;
     }
     k<<<pl.ts_grid, TsG::THREADS, pl.ts_smem, st>>>(sp);
@@ -732,10 +732,10 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
             p.algo = 2;
             p.ts_strip_w = sw;
             p.ts_grid = (int)std::max<long>(1, std::min<long>(prop.multiProcessorCount, (long)NS2 * CY / 4));
-            p.ts_slots = 3;
+            p.ts_slots = 6;          // 2-row slots: 6 x 24.1 KiB
             if (const char* se = std::getenv("B2C_TS_SLOTS")) {
                 const int v = std::atoi(se);
-                if (v >= 2 && v <= 3) p.ts_slots = v;
+                if (v >= 2 && v <= 6) p.ts_slots = v;
             }
             p.ts_smem = R == 2 ? ts_smem_bytes<2, kTsCpt, kTsWarps>(p.ts_slots)
                                : ts_smem_bytes<3, kTsCpt, kTsWarps>(p.ts_slots);

@@ -41,9 +41,12 @@
 namespace b200 {
 namespace stencil {
 
-constexpr int kTsChunkH = 4;         // rows per ring slot == granularity of the segments
+constexpr int kTsChunkH = 4;         // rows per chunk == granularity of the segments
+constexpr int kTsSlotRows = 2;       // rows per ring slot (finer than a chunk: slots are handed back,
+                                     // and refilled, twice per chunk)
 constexpr int kTsRA = 4;             // halo columns loaded on either side (keeps 16-byte alignment)
 constexpr int kTsColStageRows = 32;  // edge-column rows staged before one burst
+constexpr int kTsOutSlots = 6;       // output rows staged in shared memory (one row per slot)
 static_assert(kTsChunkH == kChunkH, "the strip partition builder is shared");
 
 template <int CPT, int NWARPS>
@@ -51,13 +54,13 @@ struct TsGeo {
     static constexpr int CONS = NWARPS * 32;             // consumer threads
     // + a producer WARPGROUP (only its first lane works).  Registers are handed out per SM
     // sub-partition, so a 9th warp would cap every thread at 168 registers; with a whole extra
-    // warpgroup the producer side shrinks to 40 registers (setmaxnreg.dec) and the consumers grow
-    // to 232 (setmaxnreg.inc) -- the windows of three time levels need ~200.
+    // warpgroup the producer side shrinks to 72 registers (setmaxnreg.dec) and the consumers grow
+    // to 216 (setmaxnreg.inc) -- the windows of three time levels need ~200.
     static constexpr int THREADS = CONS + 128;
-    static constexpr int PRODUCER_REGS = 40, CONSUMER_REGS = 232;
+    static constexpr int PRODUCER_REGS = 72, CONSUMER_REGS = 216;
     static constexpr int SWMAX = CONS * CPT;             // widest strip (cells)
     static constexpr int PITCH = SWMAX + 2 * kTsRA;      // shared-memory row pitch (elements)
-    static constexpr int SLOT_BYTES = PITCH * kTsChunkH * 8;
+    static constexpr int SLOT_BYTES = PITCH * kTsSlotRows * 8;
     static_assert(SLOT_BYTES % 128 == 0, "slot alignment");
 };
 
@@ -70,12 +73,13 @@ struct TsParams {
     int resid;                // accumulate the residual of the last level
 };
 
-// Dynamic shared memory: nslots ring slots, then the output stage (per warp 2 halves x 2 rows of
-// 32*CPT cells), then 2*nslots mbarriers.
+// Dynamic shared memory: nslots ring slots, then the output stage (kTsOutSlots rows of SWMAX
+// cells), then the mbarriers (2 per ring slot, 2 per output slot, 1 "segment done").
 template <int T, int CPT, int NWARPS>
 constexpr size_t ts_smem_bytes(int nslots) {
-    return (size_t)nslots * TsGeo<CPT, NWARPS>::SLOT_BYTES + (size_t)4 * TsGeo<CPT, NWARPS>::SWMAX * 8 +
-           2 * (size_t)nslots * sizeof(uint64_t);
+    return (size_t)nslots * TsGeo<CPT, NWARPS>::SLOT_BYTES +
+           (size_t)kTsOutSlots * TsGeo<CPT, NWARPS>::SWMAX * 8 +
+           (2 * (size_t)nslots + 2 * kTsOutSlots + 1) * sizeof(uint64_t);
 }
 
 // T: ghost width of the plan (= levels of a full sweep); LV: levels computed by THIS sweep
@@ -84,15 +88,20 @@ template <int T, int LV, int CPT, int NWARPS>
 __global__ void __launch_bounds__(TsGeo<CPT, NWARPS>::THREADS, 1)
 stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
     using G = TsGeo<CPT, NWARPS>;
-    constexpr int CH = kTsChunkH, RA = kTsRA;
+    constexpr int CH = kTsChunkH, SR = kTsSlotRows, RA = kTsRA;
+    static_assert(CH % SR == 0 && SR % 2 == 0, "slot rows");
     static_assert(T >= 2 && T <= 4 && LV >= 1 && LV <= T, "levels");
     static_assert(CPT % 2 == 0 && CPT >= T && RA >= T, "columns per thread");
     const LaunchParams& P = SP.lp;
     extern __shared__ __align__(128) unsigned char smem[];
     const int nslots = SP.nslots;
     double* ostage = reinterpret_cast<double*>(smem + (size_t)nslots * G::SLOT_BYTES);
-    uint64_t* full = reinterpret_cast<uint64_t*>(ostage + 4 * G::SWMAX);
+    uint64_t* full = reinterpret_cast<uint64_t*>(ostage + kTsOutSlots * G::SWMAX);
     uint64_t* empty = full + nslots;
+    uint64_t* ofull = empty + nslots;          // output slot written by all consumer warps
+    uint64_t* oempty = ofull + kTsOutSlots;    // output slot read out by the store warp
+    uint64_t* segdone = oempty + kTsOutSlots;  // consumers finished a boundary segment
+    constexpr int NOS = kTsOutSlots;
     __shared__ double red_smem[NWARPS];
     __shared__ double colstage[2][kTsColStageRows][T];   // [west|east][row][k]
 
@@ -104,14 +113,19 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
             ptx::mbar_init(&full[s], 1);
             ptx::mbar_init(&empty[s], NWARPS);
         }
+        for (int s = 0; s < NOS; ++s) {
+            ptx::mbar_init(&ofull[s], NWARPS);
+            ptx::mbar_init(&oempty[s], 1);
+        }
+        ptx::mbar_init(segdone, 1);
         ptx::fence_mbar_init();
     }
     __syncthreads();
 
     if (warp >= NWARPS) {
-        // ===================== producer: flag acquire + one bulk copy per row =====================
+        // ============ producer warp: flag acquire, one bulk copy per row, ghost-column patch ============
         ptx::setmaxnreg_dec<G::PRODUCER_REGS>();
-        if (warp == NWARPS && lane == 0) {
+        if (warp == NWARPS) {
             int slot = 0;
             uint32_t phase = 0;
             const int rows_total = P.H + 2 * P.g;
@@ -119,12 +133,11 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                 const Segment sg = SP.segs[s];
                 const unsigned act = sg.dirs;
                 if (act && !(P.debug & 2)) {
-                    const uint64_t t0 = ptx::globaltimer_ns();
-                    for (int d = 0; d < 8; ++d) {
-                        if (!(act >> d & 1u)) continue;
+                    if (lane < 8 && (act >> lane & 1u)) {      // one lane per direction
+                        const uint64_t t0 = ptx::globaltimer_ns();
                         uint32_t spins = 0;
-                        const uint64_t need = (*P.step_ctr + P.step_off) * P.signals_per_step[d];
-                        while (ptx::ld_acquire_sys(P.my_flags + d) < need) {
+                        const uint64_t need = (*P.step_ctr + P.step_off) * P.signals_per_step[lane];
+                        while (ptx::ld_acquire_sys(P.my_flags + lane) < need) {
                             if ((++spins & 1023u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
                                 atomicOr(P.status, 1u);
                                 break;
@@ -134,26 +147,103 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                     // ghost rows were written by another GPU's generic proxy; the bulk copies
                     // below read them through the async proxy
                     ptx::fence_proxy_async();
+                    __syncwarp();
                 }
                 const int x0 = sg.strip * SP.strip_w;
                 const int sw = min(SP.strip_w, P.W - x0);
-                const uint32_t row_bytes = (uint32_t)(sw + 2 * RA) * 8u;
-                const double* col0 = P.in + P.lead + x0 - RA;
+                const bool west = x0 == 0, east = x0 + sw == P.W;
+                const bool patch = (act & kColDirs) != 0;
+                // Ghost COLUMNS of an edge strip do not come from the grid but from the landing
+                // buffers: the row copies leave them out and this warp fills them in with plain
+                // stores before it arrives on the slot's barrier (the consumers see no difference).
+                const int lo = (patch && west) ? RA : 0, hi = (patch && east) ? RA : 0;
+                const uint32_t row_bytes = (uint32_t)(sw + 2 * RA - lo - hi) * 8u;
+                const double* col0 = P.in + P.lead + x0 - RA + lo;
                 for (int j = sg.j0 - 1; j <= sg.j1; ++j) {
-                    ptx::mbar_wait(&empty[slot], phase ^ 1u);
-                    // rows of the chunk that exist in the padded buffer (the chunk above the
-                    // first and below the last core chunk stick out by 4 - T rows)
-                    const int pr0 = P.g + j * CH;
-                    const int ra = max(0, -pr0), rb = min(CH, rows_total - pr0);
-                    const int nrows = max(0, rb - ra);
-                    ptx::mbar_arrive_expect_tx(&full[slot], (uint32_t)nrows * row_bytes);
-                    unsigned char* dst = smem + (size_t)slot * G::SLOT_BYTES;
-                    for (int r = ra; r < rb; ++r)
-                        ptx::bulk_load_1d(dst + (size_t)r * G::PITCH * 8,
-                                          col0 + (size_t)(pr0 + r) * P.pitch, row_bytes, &full[slot]);
-                    if (++slot == nslots) { slot = 0; phase ^= 1u; }
+#pragma unroll 1
+                    for (int h = 0; h < CH / SR; ++h) {
+                        ptx::mbar_wait(&empty[slot], phase ^ 1u);
+                        // rows of the slot that exist in the padded buffer (the chunk above the
+                        // first and below the last core chunk stick out by 4 - T rows)
+                        const int pr0 = P.g + j * CH + h * SR;
+                        const int ra = max(0, -pr0), rb = min(SR, rows_total - pr0);
+                        const int nrows = max(0, rb - ra);
+                        double* ch = reinterpret_cast<double*>(smem + (size_t)slot * G::SLOT_BYTES);
+                        if (lane == 0) {
+                            ptx::mbar_expect_tx(&full[slot], (uint32_t)nrows * row_bytes);
+                            for (int r = ra; r < rb; ++r)
+                                ptx::bulk_load_1d(ch + (size_t)r * G::PITCH + lo,
+                                                  col0 + (size_t)(pr0 + r) * P.pitch, row_bytes, &full[slot]);
+                        }
+                        if (patch) {
+                            const int e = lane;
+                            if (e < 2 * SR * T) {
+                                const int side = e / (SR * T), rem = e % (SR * T);
+                                const int r = rem / T, q = rem % T;
+                                const int pr = pr0 + r;                 // padded row
+                                if (((side == 0 && west) || (side == 1 && east)) && pr >= 0 && pr < rows_total) {
+                                    const int vd = pr < T ? (side ? NE : NW)
+                                                          : (pr >= P.H + T ? (side ? SE : SW) : (side ? E_ : W_));
+                                    const double v = (act >> vd & 1u)
+                                        ? P.my_land[side][land_index(pr, T, T) + q]
+                                        : P.in[(size_t)pr * P.pitch + P.lead + (side ? P.W + q : q - T)];
+                                    ch[r * G::PITCH + (side ? RA + sw + q : RA - T + q)] = v;
+                                }
+                            }
+                            // plain smem writes vs the bulk copy that refills this slot later
+                            ptx::fence_proxy_async_smem();
+                            __syncwarp();
+                        }
+                        if (lane == 0) ptx::mbar_arrive(&full[slot]);
+                        if (++slot == nslots) { slot = 0; phase ^= 1u; }
+                    }
                 }
             }
+        }
+        if (warp == NWARPS + 1 && lane == 0) {
+            // ============ store thread: staged output rows -> global memory (one bulk copy per
+            // row; edge rows also into the neighbour's ghost rows), then the halo signals ============
+            // The consumers never issue a global store: plain STG made the next row's arithmetic
+            // wait for the store to read its registers, per-warp bulk copies back-pressured the
+            // issuing warps (ncu, profiles/README.md).
+            uint64_t n = 0, freed = 0;          // rows issued / output slots handed back
+            uint32_t segph = 0;
+            auto free_upto = [&](uint64_t m) {
+                for (; freed < m; ++freed) ptx::mbar_arrive(&oempty[freed % NOS]);
+            };
+            for (int s = sbeg; s < send; ++s) {
+                const Segment sg = SP.segs[s];
+                const unsigned act = sg.dirs;
+                const int x0 = sg.strip * SP.strip_w;
+                const int sw = min(SP.strip_w, P.W - x0);
+                const int ylo = sg.j0 * CH, yhi = min(sg.j1 * CH, P.H);
+                const size_t col = (size_t)P.lead + x0;
+                for (int y = ylo; y < yhi; ++y, ++n) {
+                    const int os = (int)(n % NOS);
+                    ptx::mbar_wait(&ofull[os], (uint32_t)(n / NOS) & 1u);
+                    const double* src = ostage + (size_t)os * G::SWMAX;
+                    ptx::bulk_store_1d(P.out + (size_t)(y + P.g) * P.pitch + col, src, sw * 8);
+                    if ((act >> N & 1u) && y < T)
+                        ptx::bulk_store_1d(P.peer_out[N] + (size_t)(y + P.g + P.H) * P.pitch + col, src, sw * 8);
+                    if ((act >> S & 1u) && y >= P.H - T)
+                        ptx::bulk_store_1d(P.peer_out[S] + (size_t)(y + P.g - P.H) * P.pitch + col, src, sw * 8);
+                    ptx::bulk_commit();
+                    ptx::bulk_wait_read<1>();   // every row but the newest has left shared memory
+                    free_upto(n);
+                }
+                if (act) {
+                    // the consumers' own peer stores (edge columns) are done ...
+                    ptx::mbar_wait(segdone, segph);
+                    segph ^= 1u;
+                    // ... and so are my bulk copies into the neighbours' ghost rows
+                    ptx::bulk_wait<0>();
+                    free_upto(n);
+                    ptx::fence_acq_rel_sys();
+                    for (int d = 0; d < 8; ++d)
+                        if (act >> d & 1u) ptx::red_add_relaxed_sys(P.peer_flag[d], 1ull);
+                }
+            }
+            ptx::bulk_wait<0>();      // the output stage must outlive its last bulk copies
         }
         return;
     }
@@ -168,6 +258,8 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
     double racc = 0.0;
     int slot = 0;                       // mirrors the producer's ring position
     uint32_t phase = 0;
+    int os = 0;                         // mirrors the store thread's output slot
+    uint32_t ophase = 0;
     // lv[k][row % 3][col]: the three newest rows of time level k.  Level k covers columns
     // c0-(LV-k) .. c0+CPT-1+(LV-k) (level 0: the aligned window above).  All indices are
     // compile-time constants after unrolling, so the windows live in registers.
@@ -189,28 +281,6 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
         const int ylo = sg.j0 * CH, yhi = min(sg.j1 * CH, P.H);  // output rows of this segment
         int staged0 = -1;                                      // first core row held in colstage
 
-        // Ghost columns of a freshly loaded chunk come from the landing buffers.
-        auto patch_chunk = [&](int jj) {
-            double* ch = reinterpret_cast<double*>(smem + (size_t)slot * G::SLOT_BYTES);
-            bool wrote = false;
-            for (int e = tid; e < 2 * CH * T; e += G::CONS) {
-                const int side = e / (CH * T), rem = e % (CH * T);
-                const int r = rem / T, q = rem % T;
-                if ((side == 0 && !west) || (side == 1 && !east)) continue;
-                const int pr = P.g + jj * CH + r;               // padded row
-                if (pr < 0 || pr >= P.H + 2 * T) continue;
-                const int vd = pr < T ? (side ? NE : NW) : (pr >= P.H + T ? (side ? SE : SW)
-                                                                          : (side ? E_ : W_));
-                if (!(act >> vd & 1u)) continue;
-                const int col = side ? RA + sw + q : RA - T + q;
-                ch[r * G::PITCH + col] = P.my_land[side][land_index(pr, T, T) + q];
-                wrote = true;
-            }
-            // generic smem writes vs the next bulk copy into this slot (writers only: the fence
-            // is slow and the other ~230 threads have nothing to order)
-            if (wrote) ptx::fence_proxy_async_smem();
-            ptx::named_bar_sync(3, G::CONS);
-        };
         // Burst the staged edge columns [staged0, upto) into the neighbours' landing buffers.
         auto flush_cols = [&](int upto) {
             if (staged0 < 0 || upto <= staged0) return;
@@ -305,59 +375,34 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
         // every fourth row.
         const int i_begin = (sg.j0 - 1) * CH, i_end = (sg.j1 + 1) * CH;
         const double* base = nullptr;
-        // this warp's piece of an output row: columns [wcol0, wcol0 + wcells) of the strip
-        const int wcol0 = warp * 32 * CPT;
-        const int wcells = max(0, min(32 * CPT, sw - wcol0));
-        double* const ost_w = ostage + (size_t)warp * 4 * 32 * CPT;      // [half][row][32*CPT]
         auto step = [&](auto phc, auto actc, auto rsc, int i) {
             constexpr bool ACT = decltype(actc)::value;
             const int r = (i - i_begin) & (CH - 1);
-            if (r == 0) {
+            if ((r & (SR - 1)) == 0) {
                 ptx::mbar_wait(&full[slot], phase);
-                if (ACT) {
-                    const int jj = sg.j0 - 1 + ((i - i_begin) >> 2);
-                    if (patch) patch_chunk(jj);
-                    if (patch && staged0 < 0 && i - LV + CH > ylo) staged0 = max(i - LV, ylo);
-                }
                 base = reinterpret_cast<const double*>(smem + (size_t)slot * G::SLOT_BYTES) + c0;
             }
-            if ((r & 1) == 0) {
-                // the half of the output stage used two bulk groups ago has been read out
-                if (lane == 0) ptx::bulk_wait_read<1>();
-                __syncwarp();
+            if (ACT) {
+                if (r == 0 && patch && staged0 < 0 && i - LV + CH > ylo) staged0 = max(i - LV, ylo);
             }
-            row(phc, actc, rsc, base + r * G::PITCH, ost_w + r * (32 * CPT) + lane * CPT, i - LV);
-            if (r & 1) {
-                // two staged rows -> global memory (and, for edge rows, the neighbour's ghost rows)
+            const int y = i - LV;
+            const bool valid = y >= ylo && y < yhi;        // CTA-uniform
+            if (valid) ptx::mbar_wait(&oempty[os], ophase ^ 1u);
+            row(phc, actc, rsc, base + (r & (SR - 1)) * G::PITCH, ostage + (size_t)os * G::SWMAX + c0, y);
+            if (valid) {
+                // my part of the output row is staged: order it before the store thread's bulk copy
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) {
-                    if (wcells > 0) {
-#pragma unroll
-                        for (int b = 1; b >= 0; --b) {
-                            const int y = i - b - LV;
-                            if (y < ylo || y >= yhi) continue;
-                            const double* src = ost_w + (r - b) * (32 * CPT);
-                            const size_t col = (size_t)P.lead + x0 + wcol0;
-                            ptx::bulk_store_1d(P.out + (size_t)(y + P.g) * P.pitch + col, src, wcells * 8);
-                            if (ACT) {
-                                if ((act >> N & 1u) && y < T)
-                                    ptx::bulk_store_1d(P.peer_out[N] + (size_t)(y + P.g + P.H) * P.pitch + col,
-                                                       src, wcells * 8);
-                                if ((act >> S & 1u) && y >= P.H - T)
-                                    ptx::bulk_store_1d(P.peer_out[S] + (size_t)(y + P.g - P.H) * P.pitch + col,
-                                                       src, wcells * 8);
-                            }
-                        }
-                    }
-                    ptx::bulk_commit();
-                }
+                if (lane == 0) ptx::mbar_arrive(&ofull[os]);
+                if (++os == NOS) { os = 0; ophase ^= 1u; }
             }
-            if (r == CH - 1) {
+            if ((r & (SR - 1)) == SR - 1) {
                 // all shared-memory reads of this slot are done: hand it back to the producer
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&empty[slot]);
                 if (++slot == nslots) { slot = 0; phase ^= 1u; }
+            }
+            if (r == CH - 1) {
                 if (ACT) {
                     const int yend = min(i - LV + 1, yhi);
                     if (patch && staged0 >= 0 &&
@@ -384,19 +429,12 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
         }
 
         if (act) {
-            // my bulk copies into the neighbours' ghost rows have completed ...
-            if (lane == 0) ptx::bulk_wait<0>();
-            // ... and every consumer's peer stores happen-before thread 0's release
+            // every consumer's peer stores (edge columns) happen-before the store thread's release
             ptx::named_bar_sync(1, G::CONS);
-            if (tid == 0) {
-                ptx::fence_acq_rel_sys();
-                for (int d = 0; d < 8; ++d)
-                    if (act >> d & 1u) ptx::red_add_relaxed_sys(P.peer_flag[d], 1ull);
-            }
+            if (tid == 0) ptx::mbar_arrive(segdone);
         }
     }
 
-    if (lane == 0) ptx::bulk_wait<0>();      // the output stage must outlive its last bulk copies
     if (SP.resid) {
         // deterministic per-CTA partial: lanes -> warps -> thread 0
 #pragma unroll
