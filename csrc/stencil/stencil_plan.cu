@@ -732,7 +732,10 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
             p.algo = 2;
             p.ts_strip_w = sw;
             p.ts_grid = (int)std::max<long>(1, std::min<long>(prop.multiProcessorCount, (long)NS2 * CY / 4));
-            p.ts_slots = 6;          // 2-row slots: 6 x 24.1 KiB
+            // 2-row slots of 24.1 KiB.  Like the other two kernels this one is FASTER with a shallow
+            // ring (profiles/r2/tstrip_knobs.txt: 2/3/4/5/6 slots = 940/1063/1061/1034/1029 Gcell/s):
+            // ~50 KB in flight per SM is the latency x bandwidth product, more only adds queueing.
+            p.ts_slots = 3;
             if (const char* se = std::getenv("B2C_TS_SLOTS")) {
                 const int v = std::atoi(se);
                 if (v >= 2 && v <= 6) p.ts_slots = v;
