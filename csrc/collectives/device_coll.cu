@@ -21,6 +21,7 @@
 //   [1024,1536)  bar[P]       barrier epochs
 //   [1536,2048)  data[P]      epoch of pushed data (bcast/gather/scatter)
 //   [2048,2052)  CTA arrival counter (local use)    [2112,2116) status
+//   [2560,3072)  consumed[P]  last operation rank p has completely finished (back-pressure)
 //   [4096, ...)  IN[2][cap]  then OUT[2][cap]   (parity = epoch & 1)
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -40,7 +41,7 @@ namespace coll {
 
 constexpr int kMaxRanks = 64;
 constexpr size_t kOffReady = 0, kOffDone = 512, kOffBar = 1024, kOffData = 1536, kOffCounter = 2048,
-                 kOffStatus = 2112, kOffStaging = 4096;
+                 kOffStatus = 2112, kOffConsumed = 2560, kOffStaging = 4096;
 constexpr int kThreads = 256;
 
 struct Ws {
@@ -282,6 +283,21 @@ __global__ void __launch_bounds__(kThreads) pull_local_kernel(const __grid_const
         dst[b] = *reinterpret_cast<const volatile unsigned char*>(src + b);
 }
 
+// Back-pressure, appended to EVERY reduction / data-movement operation (one tiny kernel):
+// publish that this rank has completely finished operation `epoch` -- it will not read
+// IN[epoch&1] of any rank or its own OUT[epoch&1] again -- then wait until every rank has
+// finished operation epoch-1.  The staging halves alternate with the operation number (ONE
+// counter for reductions and data movement alike), so when this rank starts operation epoch+1
+// and overwrites the halves last used by epoch-1, nobody is still reading them.  Without it a
+// rank that only SENDS in rooted operations (reduce, gather, bcast root, scatter root) could run
+// two operations ahead of a slow root and overwrite data the root had not read yet.  Waiting for
+// epoch-1 (not epoch) keeps the wait off the critical path and makes the kernel safe for ranks
+// emulated on one GPU (every rank's tail of epoch-1 was enqueued before any tail of epoch).
+__global__ void tail_kernel(const __grid_constant__ Ws w, uint64_t epoch) {
+    signal_all(w, kOffConsumed, epoch);
+    if (epoch > 1) wait_all(w, kOffConsumed, epoch - 1);
+}
+
 __global__ void barrier_kernel(const __grid_constant__ Ws w, uint64_t epoch, int phases) {
     if (phases & 1) signal_all(w, kOffBar, epoch);
     if (phases & 2) wait_all(w, kOffBar, epoch);
@@ -290,8 +306,8 @@ __global__ void barrier_kernel(const __grid_constant__ Ws w, uint64_t epoch, int
 struct Plan {
     Ws ws;
     int device, sms;
-    uint64_t epoch;        // reductions
-    uint64_t data_epoch;   // push-type collectives
+    uint64_t epoch;        // operation counter: reductions AND push-type collectives (the staging
+                           // halves alternate with it, so the two families must share it)
     uint64_t bar_epoch;
 };
 
@@ -382,6 +398,12 @@ B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_
         case 6: launch_allreduce<long long>(p, out, count, op, root, algo, phases, st); break;
         default: launch_allreduce<int>(p, out, count, op, root, algo, phases, st); break;
     }
+    // last phase of this operation on this rank (two-shot: 4, one-shot / rooted: 2)
+    const int final_phase = (algo == 1 && root < 0) ? 4 : 2;
+    if (phases & final_phase) {
+        tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
+        B200_CHECK_LAUNCH();
+    }
     B2C_CATCH
 }
 
@@ -401,8 +423,8 @@ B2C_EXPORT int b2c_coll_move(b2c_coll* h, int kind, const void* sendbuf, void* r
     const size_t total = (kind == 0) ? block_bytes : block_bytes * (size_t)P;
     B200_REQUIRE(total <= p.ws.cap, ERR_COUNT, "message exceeds the collective workspace");
     cudaStream_t st = (cudaStream_t)stream;
-    if (phases & 1) p.data_epoch += 1;
-    const uint64_t epoch = p.data_epoch;
+    if (phases & 1) p.epoch += 1;
+    const uint64_t epoch = p.epoch;
     const unsigned long long all = P == 64 ? ~0ull : ((1ull << P) - 1);
     if (phases & 1) {
         PushArgs a{};
@@ -438,6 +460,8 @@ B2C_EXPORT int b2c_coll_move(b2c_coll* h, int kind, const void* sendbuf, void* r
                                                          bytes, sources, epoch);
             B200_CHECK_LAUNCH();
         }
+        tail_kernel<<<1, 64, 0, st>>>(p.ws, epoch);
+        B200_CHECK_LAUNCH();
     }
     B2C_CATCH
 }

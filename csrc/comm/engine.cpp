@@ -217,12 +217,12 @@ void Engine::finish_incoming(const std::shared_ptr<Incoming>& in) {
         fin.src = rank_;
         fin.msg_id = h.msg_id;
         fin.tag = err;
-        int spins = 0;
-        const double t0 = now_s();
-        while (!fabric_->try_push(h.src, fin, nullptr, 0)) {
-            drain_inbox();
-            idle_backoff(spins, t0);
-        }
+        // Never wait here: this function runs from inside drain_inbox() with the current record
+        // peeked but not yet released, so draining again would deliver that record twice.  The
+        // control record goes out now if the sender's ring has room, else with the next
+        // progress() of this rank (every wait, test, send, receive, barrier and finalize).
+        ctrlq_.emplace_back(h.src, fin);
+        flush_ctrl();
     } else {
         int64_t n = (int64_t)h.total_bytes;
         if (n > cap) {
@@ -281,8 +281,18 @@ bool Engine::drain_inbox() {
     return any;
 }
 
-bool Engine::push_sends() {
+bool Engine::flush_ctrl() {
     bool any = false;
+    while (!ctrlq_.empty()) {
+        if (!fabric_->try_push(ctrlq_.front().first, ctrlq_.front().second, nullptr, 0)) break;
+        ctrlq_.pop_front();
+        any = true;
+    }
+    return any;
+}
+
+bool Engine::push_sends() {
+    bool any = flush_ctrl();
     const uint64_t max_chunk = fabric_->max_chunk() - sizeof(RecordHeader);
     for (size_t d = 0; d < sendq_.size(); ++d) {
         auto& q = sendq_[d];

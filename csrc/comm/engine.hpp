@@ -112,6 +112,7 @@ public:
 
 private:
     bool push_sends();
+    bool flush_ctrl();   // FIN/ERR records that could not be pushed yet; never blocks, never drains
     bool drain_inbox();
     void deliver_first(const RecordHeader& h, const char* payload);
     void deliver_chunk(Incoming& in, const RecordHeader& h, const char* payload);
@@ -129,6 +130,7 @@ private:
     std::list<std::shared_ptr<Incoming>> unexpected_;
     std::map<std::pair<int, uint64_t>, std::shared_ptr<Incoming>> inflight_;
     std::map<uint64_t, std::shared_ptr<ReqState>> awaiting_fin_;
+    std::deque<std::pair<int, RecordHeader>> ctrlq_;   // control records waiting for ring space
     double timeout_s_ = 120.0;
 };
 

@@ -58,6 +58,11 @@ struct Params {
     unsigned int* status;
     uint64_t timeout_ns;
     uint64_t epoch;            // 1, 2, 3, ... (same on every rank)
+    // Back-pressure: before I overwrite slot [parity][me] in rank r's table, r must have finished
+    // reading it in the last earlier epoch of the same parity in which r gathered (need_ack[r],
+    // tracked by the host, 0 = never).  Readers publish the epoch they finished in ack[reader] of
+    // every rank's table (the u64 array that follows the 2*nranks slots).
+    uint64_t need_ack[kMaxRanks];
     int rank, nranks;
     int root;                  // -1: allreduce, else reduce to this rank
     int phases;                // bit0 local reduce + push, bit1 gather + sum
@@ -101,6 +106,19 @@ __device__ void exchange_and_finish(const Params& P, double local, double* sh) {
         // push my partial to every rank that needs it (one 16-byte slot each)
         for (int r = threadIdx.x; r < P.nranks; r += blockDim.x) {
             if (P.root >= 0 && r != P.root) continue;
+            if (P.need_ack[r] != 0) {
+                // rank r may still be reading this slot (a rooted reduce lets the non-root ranks
+                // run ahead of the root): wait for its acknowledgement of that epoch
+                const uint64_t* ack = reinterpret_cast<const uint64_t*>(P.my_slots + 2 * (size_t)P.nranks) + r;
+                const uint64_t t0 = ptx::globaltimer_ns();
+                uint32_t spins = 0;
+                while (ptx::ld_acquire_sys(ack) < P.need_ack[r]) {
+                    if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > P.timeout_ns) {
+                        atomicOr(P.status, 2u);
+                        break;
+                    }
+                }
+            }
             Slot* s = P.peer_slots[r] + (size_t)par * P.nranks + P.rank;
             s->value = local;
             ptx::st_release_sys(&s->epoch, P.epoch);
@@ -125,6 +143,10 @@ __device__ void exchange_and_finish(const Params& P, double local, double* sh) {
     __shared__ double vals[kMaxRanks];
     if ((int)threadIdx.x < P.nranks) vals[threadIdx.x] = v;
     __syncthreads();
+    // every slot of this epoch has been read: tell the pushers (ack[me] in THEIR tables)
+    if ((int)threadIdx.x < P.nranks)
+        ptx::st_release_sys(reinterpret_cast<uint64_t*>(P.peer_slots[threadIdx.x] + 2 * (size_t)P.nranks) + P.rank,
+                            P.epoch);
     if (threadIdx.x == 0) {
         double tot = 0.0;
         for (int r = 0; r < P.nranks; ++r) tot += vals[r];   // rank order: same bits everywhere
@@ -201,6 +223,7 @@ struct Plan {
     uint64_t epoch;
     uint64_t timeout_ns;
     bool owns_scratch;
+    uint64_t last_read[kMaxRanks][2];   // last epoch of each parity in which rank r gathered
 };
 
 }  // namespace dot
@@ -220,6 +243,7 @@ static void launch_dot(const Plan& pl, const void* x, const void* y, int64_t n, 
     for (int r = 0; r < pl.nranks; ++r) P.peer_slots[r] = pl.peer_slots[r];
     P.out = pl.out; P.status = pl.status; P.timeout_ns = pl.timeout_ns;
     P.epoch = pl.epoch; P.rank = pl.rank; P.nranks = pl.nranks; P.root = root; P.phases = phases;
+    for (int r = 0; r < pl.nranks; ++r) P.need_ack[r] = pl.last_read[r][pl.epoch & 1];
     const int grid = (phases & 1) ? pl.grid : 1;
     if (dtype == 9) dot_fused_kernel<double><<<grid, kThreads, 0, st>>>(P);
     else dot_fused_kernel<float><<<grid, kThreads, 0, st>>>(P);
@@ -232,7 +256,8 @@ extern "C" {
 B2C_EXPORT int b2c_dot_symmetric_bytes(int nranks, size_t* bytes) {
     B2C_TRY
     B200_REQUIRE(bytes && nranks >= 1 && nranks <= kMaxRanks, ERR_ARG, "bad rank count");
-    *bytes = (((size_t)2 * nranks * sizeof(Slot)) + 255) & ~(size_t)255;
+    // 2 x nranks slots {value, epoch}, then nranks acknowledgement words
+    *bytes = (((size_t)2 * nranks * sizeof(Slot)) + (size_t)nranks * sizeof(uint64_t) + 255) & ~(size_t)255;
     B2C_CATCH
 }
 
@@ -294,6 +319,9 @@ B2C_EXPORT int b2c_dot_run(b2c_dot* h, const void* x, const void* y, int64_t n, 
     Plan& p = h->p;
     if (phases & 1) p.epoch += 1;
     launch_dot(p, x, y, n, dtype, root, phases, p.partials, p.counter, (cudaStream_t)stream);
+    if (phases & 2)   // who reads its slot table in this epoch: the root, or everybody
+        for (int r = 0; r < p.nranks; ++r)
+            if (root < 0 || r == root) p.last_read[r][p.epoch & 1] = p.epoch;
     B2C_CATCH
 }
 

@@ -15,6 +15,8 @@
 //   mode 1  TMA  : cp.async.bulk global->smem, cp.async.bulk smem->peer global,
 //                  one elected thread per CTA drives a 4-stage ring
 #include <cuda_runtime.h>
+
+#include <atomic>
 #include <stdint.h>
 
 #include <algorithm>
@@ -243,11 +245,15 @@ B2C_EXPORT int b2c_p2p_put(void* dst, const void* src, size_t bytes, void* peer_
         const size_t chunks = (bytes + kTmaChunk - 1) / kTmaChunk;
         const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)max_ctas, chunks));
         const size_t smem = (size_t)kTmaStages * kTmaChunk + kTmaStages * sizeof(uint64_t);
-        static bool attr = false;
-        if (!attr) {
+        // function attributes are per DEVICE: a process that drives several GPUs must set it on
+        // each of them (setting it twice, from racing threads, is harmless)
+        static std::atomic<bool> attr_done[64];
+        int dev = 0;
+        B200_CHECK_CUDA(cudaGetDevice(&dev));
+        if (!attr_done[dev & 63]) {
             B200_CHECK_CUDA(cudaFuncSetAttribute(put_tma_kernel,
                                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr = true;
+            attr_done[dev & 63] = true;
         }
         put_tma_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(P);
     } else {

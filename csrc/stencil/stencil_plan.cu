@@ -10,6 +10,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -383,7 +384,7 @@ static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, c
     sp.box_w = pl.strip_w + 4;
     auto k0 = stencil_strip_kernel<R, false, SLOTS>;
     auto k1 = stencil_strip_kernel<R, true, SLOTS>;
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];   // per device; setting it twice is harmless
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.strip_smem));
         B200_CHECK_CUDA(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.strip_smem));
@@ -397,7 +398,7 @@ static void launch_strip_s(const Plan& pl, const LaunchParams& lp, bool resid, c
 template <int R, bool BOX, bool RESID, int NST, int TB = 0, int TH = kTileH, int LV = TB>
 static void launch_one(const Plan& pl, const LaunchParams& lp, cudaStream_t st) {
     auto k = stencil_fused_kernel<R, BOX, RESID, NST, TB, TH, LV>;
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];   // per device; setting it twice is harmless
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)pl.smem));
@@ -471,7 +472,7 @@ static void launch_ts_lv(const Plan& pl, const LaunchParams& lp, bool resid, cud
     sp.nslots = pl.ts_slots;
     sp.resid = resid ? 1 : 0;
     auto k = stencil_tstrip_kernel<T, LV, kTsCpt, kTsWarps>;
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];   // per device; setting it twice is harmless
     if (!attr_done[pl.device & 63]) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)ts_smem_bytes<T, kTsCpt, kTsWarps>(6)));
@@ -723,10 +724,7 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         const bool eligible = R <= 3 && H >= 16 && last >= R && (H % kChunkH == 0 || H % kChunkH >= R);
         const long steps_per_cta = (long)NS2 * CY / std::max(1, prop.multiProcessorCount);
         bool use = eligible && steps_per_cta >= 48;
-        if (ae && std::string(ae) == "strip") {
-            B200_REQUIRE(eligible, ERR_ARG, "temporal strip kernel not applicable to this tile");
-            use = true;
-        }
+        if (ae && std::string(ae) == "strip") use = eligible;   // whenever it applies, however small the tile
         if (ae && std::string(ae) == "tile") use = false;
         if (use) {
             p.algo = 2;

@@ -289,3 +289,105 @@ def test_dot_slot_protocol_one_parity_is_not_enough():
         except Violation:
             found += 1
     assert found > 0
+
+
+# ------------------------------------------------------------------------------------------------
+# Rooted reduce / mixed sequences: only the readers of an epoch wait, so the pushers can run ahead.
+# The kernel's rule (csrc/kernels/dot.cu): a reader publishes ack[reader] = e in every table once it
+# has read its slots of epoch e; a pusher that targets rank t in epoch e first waits for
+# ack[t] >= (last earlier epoch of the same parity in which t read).  The collectives
+# (csrc/collectives/device_coll.cu) use the coarser form of the same idea: "consumed" epochs.
+class RootedDotSim:
+    """roots[e-1] is the root of epoch e (None: allreduce).  Pushers: everybody; readers: root / all."""
+
+    def __init__(self, nranks, roots, rng, with_ack=True):
+        self.P, self.roots, self.rng, self.with_ack = nranks, roots, rng, with_ack
+        self.table = [[[0] * nranks for _ in range(2)] for _ in range(nranks)]    # [rank][parity][src]
+        self.ack = [[0] * nranks for _ in range(nranks)]                           # [table of][reader]
+        self.state = [{"e": 1, "phase": "write", "k": 0} for _ in range(nranks)]
+        # host-side bookkeeping, identical on every rank: last epoch of each parity in which r read
+        self.need = []
+        last = [[0, 0] for _ in range(nranks)]
+        for e, root in enumerate(roots, start=1):
+            self.need.append([last[t][e & 1] for t in range(nranks)])
+            for t in range(nranks):
+                if root is None or t == root:
+                    last[t][e & 1] = e
+
+    def targets(self, e):
+        root = self.roots[e - 1]
+        return list(range(self.P)) if root is None else [root]
+
+    def reads(self, r, e):
+        root = self.roots[e - 1]
+        return root is None or r == root
+
+    def run(self):
+        E = len(self.roots)
+        while any(s["e"] <= E for s in self.state):
+            ready = []
+            for r, s in enumerate(self.state):
+                if s["e"] > E:
+                    continue
+                e = s["e"]
+                if s["phase"] == "write" and self.with_ack:
+                    t = self.targets(e)[s["k"]]
+                    if self.ack[r][t] < self.need[e - 1][t]:
+                        continue
+                if s["phase"] == "wait" and any(v < e for v in self.table[r][e & 1]):
+                    continue
+                ready.append(r)
+            if not ready:
+                raise Violation("rooted dot: deadlock")
+            r = self.rng.choice(ready)
+            s = self.state[r]
+            e, p = s["e"], s["e"] & 1
+            if s["phase"] == "write":
+                tg = self.targets(e)
+                self.table[tg[s["k"]]][p][r] = e
+                s["k"] += 1
+                if s["k"] == len(tg):
+                    s["k"] = 0
+                    if self.reads(r, e):
+                        s["phase"] = "wait"
+                    else:
+                        s["e"] = e + 1
+            elif s["phase"] == "wait":
+                s["phase"] = "read"
+            elif s["phase"] == "read":
+                if self.table[r][p][s["k"]] != e:
+                    raise Violation(f"rooted dot: rank {r} epoch {e} read slot {s['k']} holding epoch "
+                                    f"{self.table[r][p][s['k']]}")
+                s["k"] += 1
+                if s["k"] == self.P:
+                    s["phase"], s["k"] = "ack", 0
+            else:                                       # publish ack[r] = e, one table per step
+                self.ack[s["k"]][r] = e
+                s["k"] += 1
+                if s["k"] == self.P:
+                    s["e"], s["phase"], s["k"] = e + 1, "write", 0
+
+
+def _root_sequences(nranks, rng):
+    yield [0] * 8                                                  # always the same root
+    yield [e % nranks for e in range(9)]                           # rotating root
+    yield [rng.choice([None] + list(range(nranks))) for _ in range(10)]   # reduce and allreduce mixed
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 8])
+def test_rooted_reduce_with_acknowledgements_is_hazard_free(nranks):
+    for seed in range(60):
+        rng = random.Random(seed)
+        for roots in _root_sequences(nranks, rng):
+            RootedDotSim(nranks, roots, rng).run()
+
+
+def test_rooted_reduce_without_acknowledgements_is_broken():
+    """What ADVICE.md (round 1) found: two parities are only enough when EVERY rank reads."""
+    found = 0
+    for seed in range(200):
+        try:
+            RootedDotSim(3, [0] * 8, random.Random(seed), with_ack=False).run()
+        except Violation:
+            found += 1
+    assert found > 0
