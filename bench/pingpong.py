@@ -16,7 +16,9 @@ paths
     device_loop                product: whole loop inside one kernel per GPU (latency floor)
     copy_engine                baseline: cudaMemcpyAsync to the peer mapping + flag kernel
     nccl                       baseline: torch.distributed send/recv (NCCL)
-    comm_sync / comm_async     MPI-like API on device tensors (rendezvous over the host fabric)
+    comm_sync / comm_async     MPI-like API on device tensors: <= 64 KiB eager through the receiver's
+                               device mailbox (put kernel + flag, no host sync), larger messages by
+                               rendezvous (descriptor over the host fabric, receiver pulls)
     host_staged[_pinned]       baseline: D2H + host transport + H2D (the reference's -DHOST_COPY)
 """
 from __future__ import annotations
@@ -37,6 +39,7 @@ import cuda_mpi_scratch_b200 as cms
 from cuda_mpi_scratch_b200 import _lib
 from cuda_mpi_scratch_b200.ops.p2p import _OFF_DATA, _OFF_FLAGS, P2PChannel
 from cuda_mpi_scratch_b200.parallel import comm as cm
+from cuda_mpi_scratch_b200.utils.timing import ClockSampler
 
 
 def iters_for(nbytes: int) -> int:
@@ -61,6 +64,8 @@ def main() -> int:
              if s <= a.max_bytes]
     ch = P2PChannel.create(world, max(sizes))
     results = []
+    sampler = ClockSampler(dev).start()       # every record carries the clocks seen while it was timed
+    sampler.wait_first(2.0)
 
     def ev_pair():
         return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -139,8 +144,10 @@ def main() -> int:
             if path == "device_loop":
                 ch.pingpong_device(peer, rank, 20, nbytes, src)          # warm-up
                 torch.cuda.synchronize(dev); world.barrier()
+                sampler.window_begin()
                 ch.pingpong_device(peer, rank, it, nbytes, src)
                 torch.cuda.synchronize(dev)
+                sampler.window_end()
                 rtt_us = ch.pingpong_time_ns() / it / 1e3
                 if rank == 0:
                     ok = bool(torch.equal(ch.recv_view(torch.float64, n), src))
@@ -150,6 +157,7 @@ def main() -> int:
                 for _ in range(3):
                     fn()
                 torch.cuda.synchronize(dev); world.barrier()
+                sampler.window_begin()
                 if host_timed:
                     t0 = time.perf_counter()
                     for _ in range(it):
@@ -166,6 +174,7 @@ def main() -> int:
                     torch.cuda.synchronize(dev)
                     rtt_us = e0.elapsed_time(e1) / it * 1e3
                     timer = "CUDA events on rank 0"
+                sampler.window_end()
                 if rank == 0:
                     got = ch.recv_view(torch.float64, n) if path.startswith(("kernel", "copy")) else back
                     ok = bool(torch.equal(got, src))
@@ -174,11 +183,14 @@ def main() -> int:
             if rank == 0:
                 rec = {"path": path, "bytes": nbytes, "iters": it, "rtt_us": round(rtt_max, 3),
                        "GBps_one_way": round(nbytes / (rtt_max * 1e-6 / 2) / 1e9, 3),
-                       "check": "PASSED" if ok else "FAILED", "timer": timer}
+                       "check": "PASSED" if ok else "FAILED", "timer": timer,
+                       "clocks": sampler.pop_window_summary()}
                 results.append(rec)
                 print(json.dumps(rec), flush=True)
             world.barrier()
         del src, back, hbuf, hpin
+    sampler.stop()
+    print(json.dumps({"rank": rank, "device_sends": cm.device_eager_stats()}), flush=True)
     if rank == 0 and a.json:
         with open(a.json, "w") as f:
             json.dump(results, f, indent=1)

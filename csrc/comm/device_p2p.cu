@@ -16,6 +16,11 @@
 #include <cuda_runtime.h>
 #include <unistd.h>
 
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <ctime>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -28,6 +33,7 @@
 #include "comm/engine.hpp"
 #include "core/capi_util.hpp"
 #include "core/handles.hpp"
+#include "kernels/ptx.cuh"
 
 namespace b200 {
 namespace packmove {
@@ -306,6 +312,356 @@ static void unpack_to_device(const void* packed, int64_t bytes, void* buf, int64
     B200_CHECK_CUDA(cudaStreamSynchronize(st));
 }
 
+// =====================================================================================
+// Eager path: small contiguous device messages through a per-rank device MAILBOX
+// =====================================================================================
+// Reference capability: the latency end of MPI_Send / MPI_Recv / MPI_Isend / MPI_Irecv on device
+// pointers (test-benchmark/mpi-pingpong-gpu.cpp:52-53,75-76, mpi-pingpong-gpu-async.cpp:64-67).
+// The rendezvous above costs a descriptor with the whole run list, an IPC lookup, a pull kernel,
+// a cudaStreamSynchronize and a FIN record per message.  Here every rank owns a mailbox in device
+// memory, published once through the fabric's DevInfo table and mapped by its peers:
+//   sender    put kernel: payload -> slot of (me -> dest) in dest's mailbox, st.release.sys of the
+//             slot's flag, then a word in pinned host memory ("buffer read, reusable");
+//             64-byte record {slot, seq, bytes} through the host ring.
+//   receiver  on the match: ONE kernel that acquires the flag, copies slot -> user buffer and
+//             writes a token into pinned host memory; the host only polls that word.
+//             An ACK record hands the slot back.
+// No cudaStreamSynchronize, no IPC work and no allocation per message.  If no slot is free or the
+// peer has not published a mailbox yet, the caller falls back to the rendezvous.
+namespace eager {
+
+constexpr int kSlots = 4;                         // per (sender, receiver) pair
+constexpr uint64_t kSlotBytes = 64 * 1024;        // largest eager message
+constexpr int kPutThreads = 512;
+
+// process-wide counters: which path device sends took (b2c_dev_eager_stats)
+static std::atomic<unsigned long long> g_n_eager{0}, g_n_too_big{0}, g_n_no_mailbox{0}, g_n_no_slot{0},
+    g_n_other_device{0};
+
+// B200COMM_EAGER_TRACE=1: host timestamps (CLOCK_MONOTONIC, comparable across processes) of the
+// steps of every eager message, printed to stderr -- where the microseconds of a small message go
+static bool trace_on() {
+    static const bool on = [] { const char* e = std::getenv("B200COMM_EAGER_TRACE"); return e && e[0] == '1'; }();
+    return on;
+}
+static double now_us() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+#define EAGER_TRACE(...) do { if (trace_on()) std::fprintf(stderr, __VA_ARGS__); } while (0)
+
+struct Mailbox {          // device memory of one rank
+    // flags[src][slot] (u64 sequence numbers, zero initialised), then the slots
+    static size_t ctrl_bytes(int n) { return ((size_t)n * kSlots * 8 + 4095) & ~(size_t)4095; }
+    static size_t bytes(int n) { return ctrl_bytes(n) + (size_t)n * kSlots * kSlotBytes; }
+    static size_t flag_off(int src, int slot) { return ((size_t)src * kSlots + slot) * 8; }
+    static size_t slot_off(int n, int src, int slot) {
+        return ctrl_bytes(n) + ((size_t)src * kSlots + slot) * kSlotBytes;
+    }
+};
+
+// payload -> peer slot; then publish: flag in the PEER's memory (release), word in MY pinned memory
+__global__ void __launch_bounds__(kPutThreads) eager_put_kernel(const unsigned char* __restrict__ src,
+                                                                unsigned char* dst, uint64_t bytes,
+                                                                uint64_t* flag, uint64_t seq,
+                                                                volatile uint64_t* host_sent) {
+    if (((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0) {
+        const uint64_t nv = bytes / 16;
+        for (uint64_t i = threadIdx.x; i < nv; i += blockDim.x)
+            reinterpret_cast<int4*>(dst)[i] = reinterpret_cast<const int4*>(src)[i];
+        for (uint64_t b = nv * 16 + threadIdx.x; b < bytes; b += blockDim.x) dst[b] = src[b];
+    } else {
+        for (uint64_t b = threadIdx.x; b < bytes; b += blockDim.x) dst[b] = src[b];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::fence_acq_rel_sys();
+        ptx::st_relaxed_sys(flag, seq);
+        ptx::st_release_sys(const_cast<uint64_t*>(host_sent), seq);
+    }
+}
+
+// acquire the slot's flag, slot -> user buffer, token -> pinned host word
+__global__ void __launch_bounds__(kPutThreads) eager_copyout_kernel(const uint64_t* flag, uint64_t seq,
+                                                                    const unsigned char* slot,
+                                                                    unsigned char* dst, uint64_t bytes,
+                                                                    volatile uint64_t* host_token,
+                                                                    uint64_t token, uint64_t timeout_ns) {
+    if (threadIdx.x == 0 && flag != nullptr) {
+        const uint64_t t0 = ptx::globaltimer_ns();
+        uint32_t spins = 0;
+        while (ptx::ld_acquire_sys(flag) < seq)
+            if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > timeout_ns) break;
+    }
+    __syncthreads();
+    if (dst != nullptr) {
+        if (((((uintptr_t)slot) | ((uintptr_t)dst)) & 15) == 0) {
+            const uint64_t nv = bytes / 16;
+            for (uint64_t i = threadIdx.x; i < nv; i += blockDim.x)
+                reinterpret_cast<int4*>(dst)[i] = __ldcv(reinterpret_cast<const int4*>(slot) + i);
+            for (uint64_t b = nv * 16 + threadIdx.x; b < bytes; b += blockDim.x)
+                dst[b] = *reinterpret_cast<const volatile unsigned char*>(slot + b);
+        } else {
+            for (uint64_t b = threadIdx.x; b < bytes; b += blockDim.x)
+                dst[b] = *reinterpret_cast<const volatile unsigned char*>(slot + b);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && host_token != nullptr) {
+        ptx::fence_acq_rel_sys();
+        ptx::st_release_sys(const_cast<uint64_t*>(host_token), token);
+    }
+}
+
+struct HostDst {          // receive into host memory / typed device layout: finished on the host side
+    uint64_t token;
+    const unsigned char* slot;
+    void* buf;
+    int64_t count;
+    Datatype type;
+    int64_t bytes;
+    bool dst_is_device;
+};
+
+struct State {
+    int me = -1, nranks = 0, device = -1;
+    unsigned char* mailbox = nullptr;            // mine
+    unsigned char* peer_box[comm::kMaxRanks] = {};   // peers' mailboxes as mapped here (lazily)
+    bool peer_same_gpu[comm::kMaxRanks] = {};
+    bool peer_tried[comm::kMaxRanks] = {};
+    uint64_t* host_words = nullptr;              // pinned, device visible: sent[nranks], token
+    uint64_t next_seq[comm::kMaxRanks] = {};     // per destination
+    bool slot_busy[comm::kMaxRanks][kSlots] = {};
+    uint64_t slot_seq[comm::kMaxRanks][kSlots] = {};   // last sequence number written to each slot
+    uint64_t next_token = 0;
+    uint64_t traced_sent[comm::kMaxRanks] = {};
+    uint64_t traced_token = 0;
+    std::vector<HostDst> host_dsts;
+    unsigned char uuid[16] = {};
+    cudaStream_t stream = nullptr;
+};
+
+static void device_uuid(int device, unsigned char out[16]) {
+    cudaDeviceProp pr;
+    B200_CHECK_CUDA(cudaGetDeviceProperties(&pr, device));
+    std::memcpy(out, &pr.uuid, 16);
+}
+
+struct DeviceGuard {       // run with `device` current, restore the caller's device afterwards
+    int prev = -1;
+    explicit DeviceGuard(int device) {
+        B200_CHECK_CUDA(cudaGetDevice(&prev));
+        if (prev != device) B200_CHECK_CUDA(cudaSetDevice(device));
+        else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// Create this rank's mailbox on `device` and publish it (first device send / receive).
+static State& get_state(void** st, comm::Fabric* f, int me, int device) {
+    if (*st) return *static_cast<State*>(*st);
+    auto* S = new State();
+    S->me = me;
+    S->nranks = f->nranks();
+    S->device = device;
+    DeviceGuard g(device);
+    const size_t bytes = Mailbox::bytes(S->nranks);
+    B200_CHECK_CUDA(cudaMalloc(&S->mailbox, bytes));
+    B200_CHECK_CUDA(cudaMemset(S->mailbox, 0, Mailbox::ctrl_bytes(S->nranks)));
+    B200_CHECK_CUDA(cudaHostAlloc(&S->host_words, (size_t)(S->nranks + 1) * 8,
+                                  cudaHostAllocMapped | cudaHostAllocPortable));
+    std::memset(S->host_words, 0, (size_t)(S->nranks + 1) * 8);
+    S->stream = pull_stream(device);
+    device_uuid(device, S->uuid);
+    B200_CHECK_CUDA(cudaDeviceSynchronize());
+    comm::DevInfo* di = f->dev_info(me);
+    di->device = device;
+    di->pid = (int64_t)getpid();
+    di->base = (uint64_t)(uintptr_t)S->mailbox;
+    di->bytes = bytes;
+    std::memcpy(di->gpu_uuid, S->uuid, 16);
+    std::memset(di->ipc_handle, 0, sizeof(di->ipc_handle));
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, S->mailbox) == cudaSuccess) std::memcpy(di->ipc_handle, &h, sizeof(h));
+    else cudaGetLastError();           // not exportable: only peers inside this process can use it
+    di->ready.store(1, std::memory_order_release);
+    *st = S;
+    return *S;
+}
+
+static void prepare(void** st, comm::Fabric* f, int me, int device) { get_state(st, f, me, device); }
+
+// Rank `r`'s mailbox as addressable from my device, or nullptr (not published / not mappable).
+static unsigned char* map_peer(State& S, comm::Fabric* f, int r) {
+    if (S.peer_box[r]) return S.peer_box[r];
+    if (S.peer_tried[r]) return nullptr;
+    if (r == S.me) {
+        S.peer_box[r] = S.mailbox;
+        S.peer_same_gpu[r] = true;
+        return S.mailbox;
+    }
+    comm::DevInfo* di = f->dev_info(r);
+    if (di->ready.load(std::memory_order_acquire) != 1) return nullptr;   // ask again next time
+    if ((size_t)di->bytes != Mailbox::bytes(S.nranks)) { S.peer_tried[r] = true; return nullptr; }
+    S.peer_same_gpu[r] = std::memcmp(di->gpu_uuid, S.uuid, 16) == 0;
+    void* p = nullptr;
+    if (di->pid == (int64_t)getpid()) {
+        if (di->device != S.device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(di->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                S.peer_tried[r] = true;
+                return nullptr;
+            }
+            cudaGetLastError();
+        }
+        p = reinterpret_cast<void*>((uintptr_t)di->base);
+    } else {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, di->ipc_handle, sizeof(h));
+        bool zero = true;
+        for (size_t i = 0; i < sizeof(h); ++i) zero = zero && di->ipc_handle[i] == 0;
+        if (zero || cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            S.peer_tried[r] = true;
+            return nullptr;
+        }
+    }
+    S.peer_box[r] = static_cast<unsigned char*>(p);
+    return S.peer_box[r];
+}
+
+static bool send(void** st, comm::Fabric* f, int me, int dest, const void* buf, int device,
+                 uint64_t bytes, comm::DevEagerMsg* m, bool* gated) {
+    static const bool off = [] { const char* e = std::getenv("B200COMM_NO_EAGER"); return e && e[0] == '1'; }();
+    if (off || bytes == 0 || bytes > kSlotBytes) { ++g_n_too_big; return false; }
+    const double t_in = trace_on() ? now_us() : 0.0;
+    State& S = get_state(st, f, me, device);
+    if (device != S.device) { ++g_n_other_device; return false; }   // second GPU of a multi-device process
+    DeviceGuard g(S.device);
+    unsigned char* box = map_peer(S, f, dest);
+    if (!box) { ++g_n_no_mailbox; return false; }
+    int slot = -1;
+    // slots are used round robin so that the receiver's flags only ever grow
+    for (int k = 0; k < kSlots; ++k) {
+        const int c = (int)((S.next_seq[dest] + k) % kSlots);
+        if (!S.slot_busy[dest][c]) { slot = c; break; }
+    }
+    if (slot < 0) { ++g_n_no_slot; return false; }   // receiver is behind: rendezvous (no buffering limit)
+    const uint64_t seq = ++S.next_seq[dest];
+    S.slot_busy[dest][slot] = true;
+    S.slot_seq[dest][slot] = seq;
+    eager_put_kernel<<<1, bytes <= 2048 ? 128 : kPutThreads, 0, S.stream>>>(
+        static_cast<const unsigned char*>(buf), box + Mailbox::slot_off(S.nranks, me, slot), bytes,
+        reinterpret_cast<uint64_t*>(box + Mailbox::flag_off(me, slot)), seq, S.host_words + dest);
+    B200_CHECK_LAUNCH();
+    m->slot = (uint32_t)slot;
+    m->seq = seq;
+    m->bytes = bytes;
+    *gated = S.peer_same_gpu[dest];
+    m->flags = *gated ? 1u : 0u;
+    ++g_n_eager;
+    EAGER_TRACE("[eager %d->%d seq %llu] send: enter %.1f launched %.1f\n", me, dest,
+                (unsigned long long)seq, t_in, now_us());
+    return true;
+}
+
+static bool sent(void* st, int dest, uint64_t seq) {
+    State& S = *static_cast<State*>(st);
+    const bool ok = reinterpret_cast<volatile uint64_t*>(S.host_words)[dest] >= seq;
+    if (ok && trace_on() && S.traced_sent[dest] < seq) {
+        S.traced_sent[dest] = seq;
+        EAGER_TRACE("[eager %d->%d seq %llu] send: put kernel done seen %.1f\n", S.me, dest,
+                    (unsigned long long)seq, now_us());
+    }
+    return ok;
+}
+
+static void ack(void* st, int dest, uint32_t slot) {
+    State& S = *static_cast<State*>(st);
+    if (dest >= 0 && dest < S.nranks && slot < (uint32_t)kSlots) S.slot_busy[dest][slot] = false;
+}
+
+static uint64_t recv_start(void** st, comm::Fabric* f, int me, int src, const comm::DevEagerMsg& m,
+                           void* buf, int64_t count, const Datatype& type, int dst_device,
+                           int64_t* moved) {
+    const bool dst_is_device = dst_device >= 0;
+    B200_REQUIRE(*st != nullptr, ERR_STATE, "eager device message but this rank has no mailbox");
+    (void)f; (void)me;
+    State& S = *static_cast<State*>(*st);
+    const double t_in = trace_on() ? now_us() : 0.0;
+    DeviceGuard g(S.device);
+    const int64_t cap = type.size() * count;
+    const int64_t n = std::min<int64_t>((int64_t)m.bytes, cap);
+    const unsigned char* slot = S.mailbox + Mailbox::slot_off(S.nranks, src, (int)m.slot);
+    // message announced after its put kernel had finished (same GPU): nothing to wait for
+    const uint64_t* flag = (m.flags & 1u) ? nullptr
+                                          : reinterpret_cast<const uint64_t*>(S.mailbox + Mailbox::flag_off(src, (int)m.slot));
+    const uint64_t token = ++S.next_token;
+    // contiguous destination on my mailbox's GPU: the copy-out kernel writes it directly
+    const bool direct = dst_device == S.device && type.contiguous_layout();
+    eager_copyout_kernel<<<1, n <= 2048 ? 128 : kPutThreads, 0, S.stream>>>(flag, m.seq, slot,
+                                                          direct ? static_cast<unsigned char*>(buf) : nullptr,
+                                                          (uint64_t)n, S.host_words + S.nranks, token,
+                                                          20ull * 1000 * 1000 * 1000);
+    B200_CHECK_LAUNCH();
+    if (!direct) S.host_dsts.push_back(HostDst{token, slot, buf, count, type, n, dst_is_device});
+    EAGER_TRACE("[eager %d->%d seq %llu] recv: matched %.1f copy-out launched %.1f (token %llu)\n", src, S.me,
+                (unsigned long long)m.seq, t_in, now_us(), (unsigned long long)token);
+    *moved = n;
+    return token;
+}
+
+static bool recv_done(void* st, uint64_t token) {
+    State& S = *static_cast<State*>(st);
+    if (reinterpret_cast<volatile uint64_t*>(S.host_words)[S.nranks] < token) return false;
+    if (trace_on() && S.traced_token < token) {
+        S.traced_token = token;
+        EAGER_TRACE("[eager ->%d] recv: token %llu seen %.1f\n", S.me, (unsigned long long)token, now_us());
+    }
+    for (size_t i = 0; i < S.host_dsts.size(); ++i) {
+        if (S.host_dsts[i].token != token) continue;
+        // typed or host destination: the payload has landed in the slot; finish from here
+        HostDst d = S.host_dsts[i];
+        S.host_dsts.erase(S.host_dsts.begin() + (long)i);
+        DeviceGuard g(S.device);
+        if (d.dst_is_device) {
+            std::vector<Run> srun = {{0, d.bytes}};
+            typed_move(d.slot, srun, d.buf, d.type.flatten(d.count), S.stream);
+            B200_CHECK_CUDA(cudaStreamSynchronize(S.stream));
+        } else if (d.bytes > 0) {
+            std::vector<char> host((size_t)d.bytes);
+            B200_CHECK_CUDA(cudaMemcpyAsync(host.data(), d.slot, (size_t)d.bytes, cudaMemcpyDeviceToHost, S.stream));
+            B200_CHECK_CUDA(cudaStreamSynchronize(S.stream));
+            d.type.unpack(host.data(), d.bytes, d.buf, d.count);
+        }
+        break;
+    }
+    return true;
+}
+
+static void destroy(void* st) {
+    State* S = static_cast<State*>(st);
+    if (!S) return;
+    int prev = -1;
+    if (cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(S->device) == cudaSuccess) {
+        cudaStreamSynchronize(S->stream);
+        cudaFree(S->mailbox);
+        cudaFreeHost(S->host_words);
+        cudaSetDevice(prev);
+    }
+    cudaGetLastError();
+    delete S;
+}
+
+void stats(unsigned long long out[5]) {
+    out[0] = g_n_eager; out[1] = g_n_too_big; out[2] = g_n_no_mailbox; out[3] = g_n_no_slot;
+    out[4] = g_n_other_device;
+}
+
+}  // namespace eager
+
 struct Installer {
     Installer() {
         comm::DeviceHooks& h = comm::device_hooks();
@@ -313,6 +669,13 @@ struct Installer {
         h.export_handle = export_handle;
         h.pull = pull;
         h.unpack_to_device = unpack_to_device;
+        h.eager_prepare = eager::prepare;
+        h.eager_send = eager::send;
+        h.eager_sent = eager::sent;
+        h.eager_ack = eager::ack;
+        h.eager_recv_start = eager::recv_start;
+        h.eager_recv_done = eager::recv_done;
+        h.eager_destroy = eager::destroy;
     }
 };
 static Installer g_installer;
@@ -323,6 +686,17 @@ static Installer g_installer;
 using namespace b200;
 
 extern "C" {
+
+// How the device sends of this process travelled so far: out[0] eager (receiver's device mailbox),
+// then the reasons for the rendezvous instead: out[1] larger than a slot (or eager switched off),
+// out[2] receiver has not published / could not map a mailbox, out[3] all slots in flight,
+// out[4] buffer on another GPU than this rank's mailbox.
+B2C_EXPORT int b2c_dev_eager_stats(unsigned long long out[5]) {
+    B2C_TRY
+    B200_REQUIRE(out != nullptr, ERR_ARG, "null output");
+    devp2p::eager::stats(out);
+    B2C_CATCH
+}
 
 // Typed device-to-device move: `scount` elements of `stype` at `src` into
 // `dcount` elements of `dtype` at `dst` (either pointer may be peer mapped),

@@ -29,6 +29,12 @@ int64_t Status::count(const Datatype& t) const {
 Engine::Engine(std::shared_ptr<Fabric> f, int world_rank)
     : fabric_(std::move(f)), rank_(world_rank), sendq_((size_t)fabric_->nranks()) {}
 
+Engine::~Engine() {
+    DeviceHooks& dh = device_hooks();
+    if (dev_state_ && dh.eager_destroy) dh.eager_destroy(dev_state_);
+    dev_state_ = nullptr;
+}
+
 uint32_t Engine::alloc_contexts(uint32_t n) {
     return fabric_->header()->next_context.fetch_add(2 * n) ;
 }
@@ -65,7 +71,24 @@ std::shared_ptr<ReqState> Engine::isend(const void* buf, int64_t count, const Da
     DeviceHooks& dh = device_hooks();
     int dev = -1;
     uint64_t base = 0, alloc = 0;
-    if (bytes > 0 && dh.classify && dh.classify(buf, &dev, &base, &alloc)) {
+    DevEagerMsg em{};
+    bool gated = false;
+    const bool is_dev = bytes > 0 && dh.classify && dh.classify(buf, &dev, &base, &alloc);
+    if (is_dev && t.contiguous_layout() && dh.eager_send &&
+        dh.eager_send(&dev_state_, fabric_.get(), rank_, dest_world, buf, dev, (uint64_t)bytes, &em, &gated)) {
+        // small contiguous device buffer: a put kernel is already copying it into a slot of the
+        // receiver's device mailbox; the record only says where (no IPC handle, no run list,
+        // no host synchronisation on either side)
+        r->owned.resize(sizeof(em));
+        std::memcpy(r->owned.data(), &em, sizeof(em));
+        r->data = r->owned.data();
+        r->total = r->owned.size();
+        r->hdr.kind = REC_DEV_EAGER;
+        r->dev_eager = true;
+        r->dev_seq = em.seq;
+        r->dev_gated = gated;
+        dev_sends_.push_back(r);
+    } else if (is_dev) {
         // device buffer: ship a descriptor, the receiver pulls with a kernel
         std::vector<Run> runs = t.flatten(count);
         DevDesc d{};
@@ -127,10 +150,12 @@ std::shared_ptr<ReqState> Engine::irecv(void* buf, int64_t count, const Datatype
     r->src_world = src_world;
     r->tag = tag;
     DeviceHooks& dh = device_hooks();
-    int dev;
+    int dev = -1;
     uint64_t b, n;
     r->buf_is_device = buf && dh.classify && dh.classify(buf, &dev, &b, &n);
+    r->buf_device = r->buf_is_device ? dev : -1;
     std::lock_guard<std::recursive_mutex> lk(mu_);
+    if (r->buf_is_device && dh.eager_prepare) dh.eager_prepare(&dev_state_, fabric_.get(), rank_, dev);
     for (auto it = unexpected_.begin(); it != unexpected_.end(); ++it) {
         if (matches(*r, (*it)->first)) {
             std::shared_ptr<Incoming> in = *it;
@@ -150,7 +175,7 @@ void Engine::attach(const std::shared_ptr<ReqState>& r, const std::shared_ptr<In
     in->req = r;
     r->in = in;
     const uint64_t cap = (uint64_t)(r->type.size() * r->count);
-    in->in_place = !in->device && !r->buf_is_device && r->type.contiguous_layout() &&
+    in->in_place = !in->device && !in->eager_dev && !r->buf_is_device && r->type.contiguous_layout() &&
                    in->first.total_bytes <= cap;
     if (!in->in_place) in->data.resize((size_t)in->first.total_bytes);
 }
@@ -159,6 +184,7 @@ void Engine::deliver_first(const RecordHeader& h, const char* payload) {
     auto in = std::make_shared<Incoming>();
     in->first = h;
     in->device = h.kind == REC_DEV_RTS;
+    in->eager_dev = h.kind == REC_DEV_EAGER;
     bool matched = false;
     for (auto it = posted_.begin(); it != posted_.end(); ++it) {
         if (matches(**it, h)) {
@@ -195,6 +221,29 @@ void Engine::finish_incoming(const std::shared_ptr<Incoming>& in) {
     r->status.source = (r->inv && h.src >= 0 && h.src < (int)r->inv->size()) ? (*r->inv)[(size_t)h.src]
                                                                               : h.src;
     DeviceHooks& dh = device_hooks();
+    if (in->eager_dev) {
+        // the payload is (or will shortly be) in my device mailbox: start the copy-out and let
+        // progress_device() complete the request -- nothing here waits for the GPU
+        DevEagerMsg m;
+        std::memcpy(&m, in->data.data(), sizeof(m));
+        int64_t moved = 0;
+        r->status.error = (int64_t)m.bytes > cap ? ERR_TRUNCATE : 0;
+        try {
+            B200_REQUIRE(dh.eager_recv_start != nullptr, ERR_STATE, "device message but no device layer");
+            const uint64_t token = dh.eager_recv_start(&dev_state_, fabric_.get(), rank_, h.src, m, r->buf,
+                                                       r->count, r->type, r->buf_device, &moved);
+            r->status.bytes = moved;
+            dev_recvs_.push_back(DevRecv{in, token, m.slot});
+        } catch (const Error& e) {
+            r->status.error = e.code();
+            r->status.bytes = 0;
+            r->in.reset();
+            in->req.reset();
+            r->done.store(true, std::memory_order_release);
+        }
+        inflight_.erase({h.src, h.msg_id});
+        return;
+    }
     if (in->device) {
         DevDesc d;
         std::memcpy(&d, in->data.data(), sizeof(d));
@@ -255,7 +304,10 @@ bool Engine::drain_inbox() {
     const char* payload = nullptr;
     while (fabric_->peek(rank_, &h, &payload)) {
         any = true;
-        if (h.kind == REC_DEV_FIN || h.kind == REC_DEV_ERR) {
+        if (h.kind == REC_DEV_ACK) {
+            DeviceHooks& dh = device_hooks();
+            if (dh.eager_ack && dev_state_) dh.eager_ack(dev_state_, h.src, (uint32_t)h.tag);
+        } else if (h.kind == REC_DEV_FIN || h.kind == REC_DEV_ERR) {
             auto it = awaiting_fin_.find(h.msg_id);
             if (it != awaiting_fin_.end()) {
                 std::shared_ptr<ReqState> r = it->second;
@@ -299,6 +351,12 @@ bool Engine::push_sends() {
         while (!q.empty()) {
             std::shared_ptr<ReqState>& r = q.front();
             bool blocked = false;
+            if (r->dev_gated && r->sent == 0) {
+                // same physical GPU on both ends: announce the message only when its put kernel
+                // has finished (later messages to this rank queue up behind it: order is kept)
+                DeviceHooks& dh = device_hooks();
+                if (!dh.eager_sent(dev_state_, r->dest_world, r->dev_seq)) break;
+            }
             do {
                 const uint64_t n = std::min<uint64_t>(max_chunk, r->total - r->sent);
                 RecordHeader h = r->hdr;
@@ -311,7 +369,9 @@ bool Engine::push_sends() {
                 any = true;
             } while (r->sent < r->total);
             if (blocked) break;
-            if (!r->wait_fin) {
+            if (r->dev_eager) {
+                r->hdr_pushed = true;          // completes in progress_device()
+            } else if (!r->wait_fin) {
                 r->owned.clear();
                 r->owned.shrink_to_fit();
                 r->done.store(true, std::memory_order_release);
@@ -322,12 +382,51 @@ bool Engine::push_sends() {
     return any;
 }
 
+bool Engine::progress_device() {
+    if (dev_sends_.empty() && dev_recvs_.empty()) return false;
+    DeviceHooks& dh = device_hooks();
+    bool any = false;
+    // copy-outs complete in launch order (one stream)
+    while (!dev_recvs_.empty() && dh.eager_recv_done(dev_state_, dev_recvs_.front().token)) {
+        DevRecv d = dev_recvs_.front();
+        dev_recvs_.pop_front();
+        std::shared_ptr<ReqState> r = d.in->req;
+        RecordHeader ack{};
+        ack.kind = REC_DEV_ACK;
+        ack.src = rank_;
+        ack.tag = (int32_t)d.slot;
+        ack.msg_id = d.in->first.msg_id;
+        ctrlq_.emplace_back(d.in->first.src, ack);      // the sender may reuse the slot
+        if (r) {
+            r->in.reset();
+            d.in->req.reset();
+            r->done.store(true, std::memory_order_release);
+        }
+        any = true;
+    }
+    for (auto it = dev_sends_.begin(); it != dev_sends_.end();) {
+        ReqState& r = **it;
+        if (r.hdr_pushed && dh.eager_sent(dev_state_, r.dest_world, r.dev_seq)) {
+            r.owned.clear();
+            r.done.store(true, std::memory_order_release);
+            it = dev_sends_.erase(it);
+            any = true;
+        } else {
+            ++it;
+        }
+    }
+    if (any) flush_ctrl();
+    return any;
+}
+
 bool Engine::progress() {
     std::lock_guard<std::recursive_mutex> lk(mu_);
     bool a = push_sends();
     bool b = drain_inbox();
     bool c = b ? push_sends() : false;
-    return a || b || c;
+    bool d = progress_device();
+    if (d && !sendq_.empty()) c = push_sends() || c;   // a gated record may be free to go now
+    return a || b || c || d;
 }
 
 void Engine::idle_backoff(int& spins, double t0) {
@@ -377,6 +476,11 @@ bool Engine::iprobe(int src_world, int tag, uint32_t context, Status* st,
             DevDesc d;
             std::memcpy(&d, in->data.data(), sizeof(d));
             bytes = d.total_bytes;
+        } else if (in->eager_dev) {
+            if (in->received < sizeof(DevEagerMsg)) return false;
+            DevEagerMsg m;
+            std::memcpy(&m, in->data.data(), sizeof(m));
+            bytes = (int64_t)m.bytes;
         }
         if (st) {
             st->source = (inv && in->first.src < (int)inv->size()) ? (*inv)[(size_t)in->first.src]

@@ -35,13 +35,23 @@ struct DevDesc {
     int64_t total_bytes;    // payload bytes
 };
 
+// Payload of a REC_DEV_EAGER record: where the (contiguous, packed) message sits in the
+// receiver's device mailbox.
+struct DevEagerMsg {
+    uint32_t slot;          // slot of the (sender -> receiver) ring
+    uint32_t flags;         // bit0: the put kernel had already finished when the record was pushed
+    uint64_t seq;           // the slot's flag reaches this value when the payload has landed
+    uint64_t bytes;
+};
+
 struct Incoming {
     RecordHeader first{};
     std::vector<char> data;      // assembled payload when not received in place
     uint64_t received = 0;
     std::shared_ptr<ReqState> req;
     bool in_place = false;
-    bool device = false;
+    bool device = false;         // REC_DEV_RTS: rendezvous, the receiver pulls
+    bool eager_dev = false;      // REC_DEV_EAGER: payload already in my device mailbox
     bool complete = false;
 };
 
@@ -59,6 +69,11 @@ struct ReqState {
     std::vector<char> owned;
     uint64_t total = 0, sent = 0;
     bool wait_fin = false;           // device send: completes on REC_DEV_FIN
+    bool dev_eager = false;          // small device send through the receiver's mailbox: completes
+                                     // when the put kernel has read the buffer AND the record is out
+    bool hdr_pushed = false;
+    uint64_t dev_seq = 0;            // sequence number of that put (per destination)
+    bool dev_gated = false;          // the record may only leave once the put kernel has finished
     // ---- recv side ----
     void* buf = nullptr;
     int64_t count = 0;
@@ -67,6 +82,7 @@ struct ReqState {
     int src_world = ANY_SOURCE;
     int tag = ANY_TAG;
     bool buf_is_device = false;
+    int buf_device = -1;             // CUDA device of `buf` (known from the classification at irecv)
     std::shared_ptr<Incoming> in;
 };
 
@@ -83,12 +99,31 @@ struct DeviceHooks {
     // host message -> device buffer
     void (*unpack_to_device)(const void* packed, int64_t bytes, void* buf, int64_t count,
                              const Datatype& type) = nullptr;
+    // ---- eager path for small contiguous device messages (kernel-initiated, no host sync) ----
+    // `state` is per Engine, created on first use.  All calls come from the engine's owner thread.
+    // publish my mailbox (first device send / receive of this rank)
+    void (*eager_prepare)(void** state, Fabric* f, int me, int device) = nullptr;
+    // sender: put `bytes` at `buf` into a free slot of dest's mailbox.  false -> use the rendezvous.
+    // *gated: sender and receiver share one physical GPU, so the receiver must not be told before
+    // the put kernel has FINISHED (kernels of two ranks on one GPU must never wait for each other).
+    bool (*eager_send)(void** state, Fabric* f, int me, int dest, const void* buf, int device,
+                       uint64_t bytes, DevEagerMsg* m, bool* gated) = nullptr;
+    bool (*eager_sent)(void* state, int dest, uint64_t seq) = nullptr;    // put kernel done?
+    void (*eager_ack)(void* state, int dest, uint32_t slot) = nullptr;    // receiver freed the slot
+    // receiver: start moving message `m` from `src` out of my mailbox into (buf, count, type);
+    // returns a token for eager_recv_done.  Never blocks.
+    uint64_t (*eager_recv_start)(void** state, Fabric* f, int me, int src, const DevEagerMsg& m,
+                                 void* buf, int64_t count, const Datatype& type, int dst_device /* -1: host */,
+                                 int64_t* moved) = nullptr;
+    bool (*eager_recv_done)(void* state, uint64_t token) = nullptr;
+    void (*eager_destroy)(void* state) = nullptr;
 };
 DeviceHooks& device_hooks();
 
 class Engine {
 public:
     Engine(std::shared_ptr<Fabric> f, int world_rank);
+    ~Engine();
     int rank() const { return rank_; }
     int size() const { return fabric_->nranks(); }
     Fabric& fabric() { return *fabric_; }
@@ -113,6 +148,7 @@ public:
 private:
     bool push_sends();
     bool flush_ctrl();   // FIN/ERR records that could not be pushed yet; never blocks, never drains
+    bool progress_device();   // completions of eager device sends / receives
     bool drain_inbox();
     void deliver_first(const RecordHeader& h, const char* payload);
     void deliver_chunk(Incoming& in, const RecordHeader& h, const char* payload);
@@ -131,6 +167,11 @@ private:
     std::map<std::pair<int, uint64_t>, std::shared_ptr<Incoming>> inflight_;
     std::map<uint64_t, std::shared_ptr<ReqState>> awaiting_fin_;
     std::deque<std::pair<int, RecordHeader>> ctrlq_;   // control records waiting for ring space
+    // eager device path
+    void* dev_state_ = nullptr;
+    struct DevRecv { std::shared_ptr<Incoming> in; uint64_t token; uint32_t slot; };
+    std::deque<std::shared_ptr<ReqState>> dev_sends_;   // put launched, not yet complete
+    std::deque<DevRecv> dev_recvs_;                     // copy-out launched, not yet complete
     double timeout_s_ = 120.0;
 };
 

@@ -18,8 +18,12 @@
 namespace b200 {
 namespace comm {
 
-static size_t region_size(int nranks, size_t ring_bytes) {
+// header | nranks x (Inbox + ring) | 4 KiB slack | nranks x DevInfo (zero = not published)
+static size_t rings_end(int nranks, size_t ring_bytes) {
     return sizeof(FabricHeader) + (size_t)nranks * (sizeof(Inbox) + ring_bytes) + 4096;
+}
+static size_t region_size(int nranks, size_t ring_bytes) {
+    return rings_end(nranks, ring_bytes) + (size_t)nranks * sizeof(DevInfo) + 64;
 }
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -43,6 +47,9 @@ static void init_region(char* base, int nranks, size_t ring_bytes, size_t bytes)
         ib->tail.store(0);
         p += sizeof(Inbox) + ring_bytes;
     }
+    // device-mailbox table: all zero = nobody has published yet
+    char* tab = base + align_up(rings_end(nranks, ring_bytes), 64);
+    std::memset(tab, 0, (size_t)(base + bytes - tab));
     h->magic.store(kFabricMagic, std::memory_order_release);
 }
 
@@ -51,6 +58,10 @@ Inbox* Fabric::inbox(int r) const {
     return reinterpret_cast<Inbox*>(p);
 }
 char* Fabric::ring(int r) const { return reinterpret_cast<char*>(inbox(r)) + sizeof(Inbox); }
+DevInfo* Fabric::dev_info(int r) const {
+    char* p = base_ + align_up(rings_end((int)hdr_->nranks, hdr_->ring_bytes), 64);
+    return reinterpret_cast<DevInfo*>(p) + r;
+}
 
 Fabric* Fabric::create_local(int nranks, size_t ring_bytes) {
     B200_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, ERR_ARG, "rank count out of range");

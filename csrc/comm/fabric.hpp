@@ -26,6 +26,8 @@ enum RecordKind : uint32_t {
     REC_DEV_RTS = 2,   // device send: descriptor of the source buffer
     REC_DEV_FIN = 3,   // device send completed by the receiver (control)
     REC_DEV_ERR = 4,   // receiver could not complete the device send (control)
+    REC_DEV_EAGER = 5, // small device send: the payload sits in a slot of the receiver's device mailbox
+    REC_DEV_ACK = 6,   // receiver has emptied a mailbox slot (control; slot index in `tag`)
 };
 
 struct alignas(16) RecordHeader {
@@ -68,6 +70,21 @@ struct FabricHeader {
     char pad[64];
 };
 
+// What a rank publishes about its DEVICE mailbox (csrc/comm/device_p2p.cu) so that peers can
+// map it and put small device messages straight into it.  Lives in the shared region, all zero
+// until the rank touches a device buffer for the first time.
+struct alignas(64) DevInfo {
+    std::atomic<uint32_t> ready;      // 1 once every other field is valid
+    int32_t device;                   // owner's CUDA device index
+    int64_t pid;                      // owner process
+    uint64_t base;                    // owner-side address of the mailbox
+    uint64_t bytes;
+    unsigned char gpu_uuid[16];       // physical GPU (same-GPU peers must not wait for each other's kernels)
+    unsigned char ipc_handle[64];
+    char pad[16];
+};
+static_assert(sizeof(DevInfo) == 128, "DevInfo is two cache lines");
+
 class Fabric {
 public:
     // Heap-backed region for `nranks` threads of this process.
@@ -93,6 +110,7 @@ public:
     void release(int rank, const RecordHeader& h);
 
     void startup_barrier(int rank);
+    DevInfo* dev_info(int r) const;   // rank r's entry of the device-mailbox table
 
 private:
     Fabric() = default;

@@ -27,8 +27,12 @@ def main(argv=None) -> int:
     job = f"b200job-{os.getpid()}-{int(time.time())}"
     procs = []
     for r in range(a.nranks):
+        # LOCAL_RANK for this library; the MVAPICH2 / Open MPI names because unmodified MPI + CUDA
+        # programs pick their GPU from them BEFORE MPI_Init (the reference's BindDevice,
+        # stencil2d/mpi-2d-stencil-subarray-cuda.cu:40-73, reads MV2_COMM_WORLD_LOCAL_RANK)
         env = dict(os.environ, B200_RANK=str(r), B200_WORLD_SIZE=str(a.nranks), B200_JOB=job,
-                   LOCAL_RANK=str(r))
+                   LOCAL_RANK=str(r), MV2_COMM_WORLD_LOCAL_RANK=str(r),
+                   OMPI_COMM_WORLD_LOCAL_RANK=str(r), MPISPAWN_LOCAL_NPROCS=str(a.nranks))
         cmd = [sys.executable, a.prog] + a.args if a.prog.endswith(".py") else [a.prog] + a.args
         procs.append(subprocess.Popen(cmd, env=env))
     t0 = time.time()

@@ -167,6 +167,15 @@ def _sync_if_cuda(buf) -> None:
         torch.cuda.current_stream(buf.device).synchronize()
 
 
+def device_eager_stats() -> dict:
+    """Which path the device sends of this process took so far (``b2c_dev_eager_stats``): small
+    contiguous device buffers go through the receiver's device mailbox (``eager``), the rest by
+    rendezvous, for the reason counted."""
+    out = (C.c_ulonglong * 5)()
+    _lib.check(_lib.lib.b2c_dev_eager_stats(out))
+    return dict(zip(("eager", "too_large", "no_mailbox", "no_slot", "other_device"), [int(v) for v in out]))
+
+
 class Request:
     """``MPI_Request``; keeps the buffer alive until completion."""
 

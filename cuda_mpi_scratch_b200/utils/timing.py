@@ -158,15 +158,29 @@ class ClockSampler:
         if getattr(self, "_windows", None) and self._windows[-1][1] is None:
             self._windows[-1][1] = len(self.rows)
 
+    def pop_window_summary(self) -> dict:
+        """Summary of the LAST closed window only, which is then forgotten: one clock record per
+        measurement when a script times many things with one sampler (``bench/*.py``)."""
+        wins = getattr(self, "_windows", [])
+        if not wins or wins[-1][1] is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        a, b = wins.pop()
+        # a window shorter than one sampling period still gets the sample that follows it
+        rows = self.rows[a:max(b, a + 1)] or self.rows[-1:]
+        return self._summarise(rows, True)
+
     def summary(self) -> dict:
-        sm, smax, power = [], [], []
-        reasons: set[str] = set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         rows = self.rows
         wins = [w for w in getattr(self, "_windows", []) if w[1] is not None and w[1] > w[0]]
         in_window = bool(wins)
         if in_window:
             rows = [r for a, b in wins for r in self.rows[a:b]]
+        return self._summarise(rows, in_window)
+
+    def _summarise(self, rows, in_window: bool) -> dict:
+        sm, smax, power = [], [], []
+        reasons: set[str] = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in rows:
             try:
                 sm.append(float(r[1]))

@@ -103,6 +103,10 @@ static int run(const Comm& world, size_t n, bool async, bool host_copy, int iter
                   << " bytes " << bytes << " round-trip avg " << avg * 1e6 << " us best " << best * 1e6
                   << " us one-way " << 2.0 * bytes / best / 1e9 << " GB/s\n"
                   << (all_good ? "PASSED" : "FAILED") << std::endl;
+        unsigned long long st[5] = {0, 0, 0, 0, 0};
+        b2c_dev_eager_stats(st);
+        std::cout << "device sends of rank 0: " << st[0] << " eager (mailbox), rendezvous: " << st[1]
+                  << " too large, " << st[2] << " no mailbox yet, " << st[3] << " no free slot" << std::endl;
     }
     world.barrier();
     B2C_OK(b2c_free(dsend));

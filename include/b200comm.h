@@ -259,6 +259,14 @@ int b2c_pingpong_device(int role, int iters, size_t bytes, const void* send_loca
                         const void* my_flag, void* peer_flag, unsigned long long base_epoch,
                         double* out_ns, void* status, unsigned long long timeout_ms, void* stream);
 
+/* Device sends through the MPI-like API: counts of the paths taken so far in this process.
+ * out[0] eager (put kernel into the receiver's device mailbox, <= 64 KiB contiguous);
+ * rendezvous because: out[1] too large / eager disabled (B200COMM_NO_EAGER=1), out[2] no mapped
+ * mailbox of the receiver yet, out[3] all slots to that receiver in flight, out[4] buffer on a
+ * different GPU than this rank's mailbox.  Reference counterpart: none (a CUDA-aware MPI hides
+ * its eager/rendezvous switch, test-benchmark/mpi-pingpong-gpu.cpp:52-53). */
+int b2c_dev_eager_stats(unsigned long long out[5]);
+
 /* ------------------------------------------------ datatype-driven device moves */
 /* Pack + move + unpack in one kernel; src and dst may be peer mapped.  Reference
  * capability: derived datatypes on device pointers handed to a CUDA-aware MPI
