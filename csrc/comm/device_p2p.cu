@@ -40,7 +40,8 @@ namespace packmove {
 void launch_uniform(const void* src, void* dst, int64_t nruns, int64_t len, int64_t sstride,
                     int64_t dstride, cudaStream_t st);
 void launch_segments(const void* src, void* dst, const Segment* dev_segs, int64_t nseg,
-                     int64_t max_len, int64_t total_items_64k, cudaStream_t st);
+                     int64_t max_len, int64_t total_items_64k, cudaStream_t st,
+                     const int64_t* dev_item_start);
 }  // namespace packmove
 
 namespace devp2p {
@@ -92,21 +93,43 @@ static bool classify(const void* p, int* device, uint64_t* base, uint64_t* bytes
     return true;
 }
 
+// Identity of the allocation behind an address (unique for the life of the process).
+using PtrAttrFn = CUresult (*)(void*, CUpointer_attribute, CUdeviceptr);
+static uint64_t buffer_id_of(uint64_t ptr) {
+    static PtrAttrFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &p, cudaEnableDefault, &q) != cudaSuccess) p = nullptr;
+        cudaGetLastError();
+        return reinterpret_cast<PtrAttrFn>(p);
+    }();
+    unsigned long long id = 0;
+    if (fn && fn(&id, CU_POINTER_ATTRIBUTE_BUFFER_ID, (CUdeviceptr)ptr) == CUDA_SUCCESS) return id;
+    return 0;
+}
+
 static void export_handle(comm::DevDesc* d) {
     d->pid = (int64_t)getpid();
+    d->buffer_id = buffer_id_of(d->base_ptr);
     std::memset(d->ipc_handle, 0, sizeof(d->ipc_handle));
-    static std::map<uint64_t, cudaIpcMemHandle_t> cache;
+    // keyed by address AND allocation identity: an address that was freed and handed out again
+    // gets a fresh handle instead of the stale one
+    static std::map<uint64_t, std::pair<uint64_t, cudaIpcMemHandle_t>> cache;
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = cache.find(d->base_ptr);
+    if (it != cache.end() && it->second.first != d->buffer_id) {
+        cache.erase(it);
+        it = cache.end();
+    }
     if (it == cache.end()) {
         cudaIpcMemHandle_t h;
         if (cudaIpcGetMemHandle(&h, reinterpret_cast<void*>((uintptr_t)d->base_ptr)) != cudaSuccess) {
             cudaGetLastError();   // not IPC-capable: only same-process receivers can pull
             return;
         }
-        it = cache.emplace(d->base_ptr, h).first;
+        it = cache.emplace(d->base_ptr, std::make_pair(d->buffer_id, h)).first;
     }
-    std::memcpy(d->ipc_handle, &it->second, sizeof(cudaIpcMemHandle_t));
+    std::memcpy(d->ipc_handle, &it->second.second, sizeof(cudaIpcMemHandle_t));
 }
 
 // ---- typed move with a small plan cache -----------------------------------------
@@ -114,6 +137,7 @@ struct MovePlan {
     bool uniform = false;
     int64_t nruns = 0, len = 0, sstride = 0, dstride = 0, s0 = 0, d0 = 0;
     Segment* dev_segs = nullptr;
+    int64_t* dev_item_start = nullptr;   // prefix sums of the 64 KiB work items per segment
     int64_t nseg = 0, max_len = 0, items = 0, total = 0;
 };
 
@@ -144,11 +168,21 @@ static uint64_t hash_runs(const std::vector<Run>& r, uint64_t h) {
 }
 
 static const MovePlan& get_plan(const std::vector<Run>& s, const std::vector<Run>& d, int device) {
-    static std::map<std::pair<uint64_t, int>, MovePlan> cache;
+    // keyed by a hash of both run lists; the lists themselves are kept and compared on a hit, so
+    // two layouts that collide get two plans instead of one silently wrong move
+    struct Entry { std::vector<Run> s, d; MovePlan plan; };
+    static std::multimap<std::pair<uint64_t, int>, Entry> cache;
     const uint64_t key = hash_runs(d, hash_runs(s, 1469598103934665603ull) ^ 0x9e3779b97f4a7c15ull);
     std::lock_guard<std::mutex> lk(g_mu);
-    auto it = cache.find({key, device});
-    if (it != cache.end()) return it->second;
+    auto same = [](const std::vector<Run>& a, const std::vector<Run>& b) {
+        if (a.size() != b.size()) return false;
+        for (size_t i = 0; i < a.size(); ++i)
+            if (a[i].disp != b[i].disp || a[i].len != b[i].len) return false;
+        return true;
+    };
+    auto range = cache.equal_range({key, device});
+    for (auto it = range.first; it != range.second; ++it)
+        if (same(it->second.s, s) && same(it->second.d, d)) return it->second.plan;
     MovePlan p;
     int64_t sn, sl, ss, s0, dn, dl, ds, d0;
     const int64_t hint_s = d.size() > 1 ? d[0].len : 0, hint_d = s.size() > 1 ? s[0].len : 0;
@@ -169,9 +203,16 @@ static const MovePlan& get_plan(const std::vector<Run>& s, const std::vector<Run
             B200_CHECK_CUDA(cudaMalloc(&p.dev_segs, segs.size() * sizeof(Segment)));
             B200_CHECK_CUDA(cudaMemcpy(p.dev_segs, segs.data(), segs.size() * sizeof(Segment),
                                        cudaMemcpyHostToDevice));
+            if (p.max_len > 256) {
+                std::vector<int64_t> start(segs.size() + 1, 0);
+                for (size_t i = 0; i < segs.size(); ++i) start[i + 1] = start[i] + (segs[i].len + 65535) / 65536;
+                B200_CHECK_CUDA(cudaMalloc(&p.dev_item_start, start.size() * sizeof(int64_t)));
+                B200_CHECK_CUDA(cudaMemcpy(p.dev_item_start, start.data(), start.size() * sizeof(int64_t),
+                                           cudaMemcpyHostToDevice));
+            }
         }
     }
-    return cache.emplace(std::make_pair(key, device), p).first->second;
+    return cache.emplace(std::make_pair(key, device), Entry{s, d, p})->second.plan;
 }
 
 static int64_t run_plan(const MovePlan& p, const void* src, void* dst, cudaStream_t st);
@@ -209,7 +250,7 @@ static int64_t run_plan(const MovePlan& p, const void* src, void* dst, cudaStrea
         packmove::launch_uniform(static_cast<const char*>(src) + p.s0, static_cast<char*>(dst) + p.d0,
                                  p.nruns, p.len, p.sstride, p.dstride, st);
     } else if (p.nseg) {
-        packmove::launch_segments(src, dst, p.dev_segs, p.nseg, p.max_len, p.items, st);
+        packmove::launch_segments(src, dst, p.dev_segs, p.nseg, p.max_len, p.items, st, p.dev_item_start);
     }
     return p.total;
 }
@@ -245,10 +286,17 @@ static const void* map_source(const comm::DevDesc& d, int my_device) {
         }
         return reinterpret_cast<const void*>((uintptr_t)d.base_ptr);
     }
-    static std::map<std::pair<int64_t, uint64_t>, void*> opened;   // (pid, base) -> mapping
+    // (pid, base) -> (allocation identity, mapping); a different identity at the same address means
+    // the sender freed and re-allocated: drop the mapping of the dead allocation and map again
+    static std::map<std::pair<int64_t, uint64_t>, std::pair<uint64_t, void*>> opened;
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = opened.find({d.pid, d.base_ptr});
-    if (it != opened.end()) return it->second;
+    if (it != opened.end()) {
+        if (it->second.first == d.buffer_id) return it->second.second;
+        cudaIpcCloseMemHandle(it->second.second);
+        cudaGetLastError();
+        opened.erase(it);
+    }
     cudaIpcMemHandle_t h;
     std::memcpy(&h, d.ipc_handle, sizeof(h));
     bool zero = true;
@@ -257,7 +305,7 @@ static const void* map_source(const comm::DevDesc& d, int my_device) {
                                   "(allocate it with cudaMalloc / the default torch allocator)");
     void* p = nullptr;
     B200_CHECK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
-    opened[{d.pid, d.base_ptr}] = p;
+    opened[{d.pid, d.base_ptr}] = {d.buffer_id, p};
     return p;
 }
 
@@ -448,6 +496,40 @@ static void device_uuid(int device, unsigned char out[16]) {
     std::memcpy(out, &pr.uuid, 16);
 }
 
+// publish a slot whose payload was written by EARLIER kernels of the same stream (typed gather)
+__global__ void eager_flag_kernel(uint64_t* flag, uint64_t seq, volatile uint64_t* host_sent) {
+    ptx::fence_acq_rel_sys();
+    ptx::st_relaxed_sys(flag, seq);
+    ptx::st_release_sys(const_cast<uint64_t*>(host_sent), seq);
+}
+__global__ void eager_token_kernel(volatile uint64_t* host_token, uint64_t token) {
+    ptx::fence_acq_rel_sys();
+    ptx::st_release_sys(const_cast<uint64_t*>(host_token), token);
+}
+
+// Flattened layout of (type, count), kept per process: the run list of a derived type is built
+// once, the move plan that belongs to it is found by the ADDRESS of this entry.
+struct TypedLayout {
+    Datatype type;                 // keeps the committed type (and so its identity) alive
+    std::vector<Run> runs;         // layout in user memory
+    std::vector<Run> packed;       // {0, bytes}
+    char send_id = 0, recv_id = 0; // two stable addresses = plan identities (gather / scatter)
+};
+static TypedLayout& typed_layout(const Datatype& t, int64_t count) {
+    static std::map<std::pair<const void*, int64_t>, TypedLayout> cache;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find({t.id(), count});
+    if (it == cache.end()) {
+        TypedLayout L;
+        L.type = t;
+        L.runs = t.flatten(count);
+        L.packed = {{0, t.size() * count}};
+        it = cache.emplace(std::make_pair(t.id(), count), std::move(L)).first;
+    }
+    return it->second;
+}
+
 struct DeviceGuard {       // run with `device` current, restore the caller's device afterwards
     int prev = -1;
     explicit DeviceGuard(int device) {
@@ -533,7 +615,7 @@ static unsigned char* map_peer(State& S, comm::Fabric* f, int r) {
 }
 
 static bool send(void** st, comm::Fabric* f, int me, int dest, const void* buf, int device,
-                 uint64_t bytes, comm::DevEagerMsg* m, bool* gated) {
+                 uint64_t bytes, const Datatype& type, int64_t count, comm::DevEagerMsg* m, bool* gated) {
     static const bool off = [] { const char* e = std::getenv("B200COMM_NO_EAGER"); return e && e[0] == '1'; }();
     if (off || bytes == 0 || bytes > kSlotBytes) { ++g_n_too_big; return false; }
     const double t_in = trace_on() ? now_us() : 0.0;
@@ -552,10 +634,20 @@ static bool send(void** st, comm::Fabric* f, int me, int dest, const void* buf, 
     const uint64_t seq = ++S.next_seq[dest];
     S.slot_busy[dest][slot] = true;
     S.slot_seq[dest][slot] = seq;
-    eager_put_kernel<<<1, bytes <= 2048 ? 128 : kPutThreads, 0, S.stream>>>(
-        static_cast<const unsigned char*>(buf), box + Mailbox::slot_off(S.nranks, me, slot), bytes,
-        reinterpret_cast<uint64_t*>(box + Mailbox::flag_off(me, slot)), seq, S.host_words + dest);
-    B200_CHECK_LAUNCH();
+    unsigned char* pslot = box + Mailbox::slot_off(S.nranks, me, slot);
+    uint64_t* pflag = reinterpret_cast<uint64_t*>(box + Mailbox::flag_off(me, slot));
+    if (type.contiguous_layout()) {
+        eager_put_kernel<<<1, bytes <= 2048 ? 128 : kPutThreads, 0, S.stream>>>(
+            static_cast<const unsigned char*>(buf), pslot, bytes, pflag, seq, S.host_words + dest);
+        B200_CHECK_LAUNCH();
+    } else {
+        // derived type: gather by the sender's layout straight into the peer's slot (the packed
+        // side is contiguous, so the NVLink stores are full lines), then publish
+        TypedLayout& L = typed_layout(type, count);
+        typed_move_cached(buf, L.runs, pslot, L.packed, &L.send_id, S.stream);
+        eager_flag_kernel<<<1, 1, 0, S.stream>>>(pflag, seq, S.host_words + dest);
+        B200_CHECK_LAUNCH();
+    }
     m->slot = (uint32_t)slot;
     m->seq = seq;
     m->bytes = bytes;
@@ -601,12 +693,21 @@ static uint64_t recv_start(void** st, comm::Fabric* f, int me, int src, const co
     const uint64_t token = ++S.next_token;
     // contiguous destination on my mailbox's GPU: the copy-out kernel writes it directly
     const bool direct = dst_device == S.device && type.contiguous_layout();
-    eager_copyout_kernel<<<1, n <= 2048 ? 128 : kPutThreads, 0, S.stream>>>(flag, m.seq, slot,
-                                                          direct ? static_cast<unsigned char*>(buf) : nullptr,
-                                                          (uint64_t)n, S.host_words + S.nranks, token,
-                                                          20ull * 1000 * 1000 * 1000);
+    // derived-type destination on my GPU, whole message fits: wait for the flag, scatter by the
+    // receiver's layout with the typed move kernel, token -- three launches, still no host sync
+    const bool scatter = !direct && dst_device == S.device && (int64_t)m.bytes == cap;
+    eager_copyout_kernel<<<1, n <= 2048 ? 128 : kPutThreads, 0, S.stream>>>(
+        flag, m.seq, slot, direct ? static_cast<unsigned char*>(buf) : nullptr, (uint64_t)n,
+        scatter ? nullptr : S.host_words + S.nranks, token, 20ull * 1000 * 1000 * 1000);
     B200_CHECK_LAUNCH();
-    if (!direct) S.host_dsts.push_back(HostDst{token, slot, buf, count, type, n, dst_is_device});
+    if (scatter) {
+        TypedLayout& L = typed_layout(type, count);
+        typed_move_cached(slot, L.packed, buf, L.runs, &L.recv_id, S.stream);
+        eager_token_kernel<<<1, 1, 0, S.stream>>>(S.host_words + S.nranks, token);
+        B200_CHECK_LAUNCH();
+    } else if (!direct) {
+        S.host_dsts.push_back(HostDst{token, slot, buf, count, type, n, dst_is_device});
+    }
     EAGER_TRACE("[eager %d->%d seq %llu] recv: matched %.1f copy-out launched %.1f (token %llu)\n", src, S.me,
                 (unsigned long long)m.seq, t_in, now_us(), (unsigned long long)token);
     *moved = n;

@@ -74,9 +74,10 @@ std::shared_ptr<ReqState> Engine::isend(const void* buf, int64_t count, const Da
     DevEagerMsg em{};
     bool gated = false;
     const bool is_dev = bytes > 0 && dh.classify && dh.classify(buf, &dev, &base, &alloc);
-    if (is_dev && t.contiguous_layout() && dh.eager_send &&
-        dh.eager_send(&dev_state_, fabric_.get(), rank_, dest_world, buf, dev, (uint64_t)bytes, &em, &gated)) {
-        // small contiguous device buffer: a put kernel is already copying it into a slot of the
+    if (is_dev && dh.eager_send &&
+        dh.eager_send(&dev_state_, fabric_.get(), rank_, dest_world, buf, dev, (uint64_t)bytes, t, count,
+                      &em, &gated)) {
+        // small device message: a put kernel is already copying (gathering) it into a slot of the
         // receiver's device mailbox; the record only says where (no IPC handle, no run list,
         // no host synchronisation on either side)
         r->owned.resize(sizeof(em));

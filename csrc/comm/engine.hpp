@@ -33,6 +33,8 @@ struct DevDesc {
     int64_t count;
     int64_t nruns;          // flattened runs of `count` elements follow the descriptor
     int64_t total_bytes;    // payload bytes
+    uint64_t buffer_id;     // CU_POINTER_ATTRIBUTE_BUFFER_ID of the allocation: a cudaFree + cudaMalloc
+                            // that returns the same address is a DIFFERENT allocation
 };
 
 // Payload of a REC_DEV_EAGER record: where the (contiguous, packed) message sits in the
@@ -106,8 +108,11 @@ struct DeviceHooks {
     // sender: put `bytes` at `buf` into a free slot of dest's mailbox.  false -> use the rendezvous.
     // *gated: sender and receiver share one physical GPU, so the receiver must not be told before
     // the put kernel has FINISHED (kernels of two ranks on one GPU must never wait for each other).
+    // `type`/`count` describe the layout at `buf`; a derived type is GATHERED by the put (the slot
+    // always holds the packed bytes), so strided data crosses NVLink as contiguous bursts.
     bool (*eager_send)(void** state, Fabric* f, int me, int dest, const void* buf, int device,
-                       uint64_t bytes, DevEagerMsg* m, bool* gated) = nullptr;
+                       uint64_t bytes, const Datatype& type, int64_t count, DevEagerMsg* m,
+                       bool* gated) = nullptr;
     bool (*eager_sent)(void* state, int dest, uint64_t seq) = nullptr;    // put kernel done?
     void (*eager_ack)(void* state, int dest, uint32_t slot) = nullptr;    // receiver freed the slot
     // receiver: start moving message `m` from `src` out of my mailbox into (buf, count, type);

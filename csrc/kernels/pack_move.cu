@@ -62,15 +62,27 @@ __device__ __forceinline__ void copy_any(char* d, const char* s, int64_t n, int 
 
 // Large segments: one CTA per (segment, 64 KiB chunk) work item.
 __global__ void segment_move_cta_kernel(const char* src, char* dst, const Segment* segs,
-                                        int64_t nseg, int64_t chunk) {
+                                        int64_t nseg, int64_t chunk, const int64_t* item_start) {
     for (int64_t item = blockIdx.x;; item += gridDim.x) {
-        // work items are enumerated segment-major; the table carries no prefix
-        // sums, so walk it (tables with large segments are short)
+        // work items are enumerated segment-major: item_start[s] = first item of segment s
+        // (prefix sums built with the plan, item_start[nseg] = number of items) -> binary search.
+        // Callers that bring their own table without prefix sums get the linear walk.
         int64_t k = item, sidx = 0;
-        for (; sidx < nseg; ++sidx) {
-            const int64_t c = (segs[sidx].len + chunk - 1) / chunk;
-            if (k < c) break;
-            k -= c;
+        if (item_start != nullptr) {
+            if (item >= item_start[nseg]) return;
+            int64_t lo = 0, hi = nseg;            // last s with item_start[s] <= item
+            while (hi - lo > 1) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (item_start[mid] <= item) lo = mid; else hi = mid;
+            }
+            sidx = lo;
+            k = item - item_start[lo];
+        } else {
+            for (; sidx < nseg; ++sidx) {
+                const int64_t c = (segs[sidx].len + chunk - 1) / chunk;
+                if (k < c) break;
+                k -= c;
+            }
         }
         if (sidx >= nseg) return;
         const Segment sg = segs[sidx];
@@ -109,7 +121,8 @@ void launch_uniform(const void* src, void* dst, int64_t nruns, int64_t len, int6
 }
 
 void launch_segments(const void* src, void* dst, const Segment* dev_segs, int64_t nseg,
-                     int64_t max_len, int64_t total_items_64k, cudaStream_t st) {
+                     int64_t max_len, int64_t total_items_64k, cudaStream_t st,
+                     const int64_t* dev_item_start) {
     if (max_len <= 256) {
         const int threads = 256;
         const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nseg + threads - 1) / threads, 148 * 8));
@@ -118,7 +131,8 @@ void launch_segments(const void* src, void* dst, const Segment* dev_segs, int64_
     } else {
         const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(total_items_64k, 148 * 4));
         segment_move_cta_kernel<<<grid, 256, 0, st>>>(static_cast<const char*>(src),
-                                                      static_cast<char*>(dst), dev_segs, nseg, 65536);
+                                                      static_cast<char*>(dst), dev_segs, nseg, 65536,
+                                                      dev_item_start);
     }
     B200_CHECK_LAUNCH();
 }
@@ -148,7 +162,7 @@ B2C_EXPORT int b2c_move_segments(const void* src, void* dst, const void* dev_seg
     B200_REQUIRE(src && dst && dev_segments && nseg >= 0, ERR_ARG, "bad argument");
     if (nseg)
         packmove::launch_segments(src, dst, static_cast<const Segment*>(dev_segments), nseg, max_len,
-                                  items_64k, (cudaStream_t)stream);
+                                  items_64k, (cudaStream_t)stream, nullptr);
     B2C_CATCH
 }
 

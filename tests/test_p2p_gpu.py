@@ -130,6 +130,88 @@ def test_comm_device_derived_types_and_mixed_host_device():
     assert out == ([5, 6, 7, 8, 12, 13],) * 3
 
 
+def test_comm_eager_and_rendezvous_paths_and_send_before_receive():
+    """Small device messages travel through the receiver's device mailbox (no IPC, no FIN): a rank
+    may therefore SEND FIRST and receive later on both sides, which a pure rendezvous would deadlock
+    on.  Larger ones, and bursts that exceed the four slots per peer, fall back to the rendezvous;
+    order per (source, tag) is kept across the two paths."""
+    def body(c):
+        torch.cuda.set_device(0)
+        peer = 1 - c.rank
+        before = cm.device_eager_stats()
+        small = torch.full((512,), float(c.rank + 1), dtype=torch.float64, device="cuda")
+        got = torch.zeros_like(small)
+        # publish both mailboxes first (a rank's mailbox appears with its first device operation)
+        r0 = c.irecv(got, peer, tag=0); s0 = c.isend(small, peer, tag=0); r0.wait(); s0.wait()
+        c.barrier()
+        c.send(small, peer, tag=1)                    # both ranks send first ...
+        c.recv(got, peer, tag=1)                      # ... and receive afterwards
+        ok = bool((got == float(peer + 1)).all())
+        # a burst of 12 messages with distinct contents, received in order
+        msgs = [torch.full((64,), float(100 * c.rank + i), dtype=torch.float64, device="cuda") for i in range(12)]
+        big = torch.arange(1 << 16, dtype=torch.float64, device="cuda") + c.rank     # 512 KiB: rendezvous
+        if c.rank == 0:
+            reqs = [c.isend(m, peer, tag=7) for m in msgs] + [c.isend(big, peer, tag=7)]
+            cm.waitall(reqs)
+        else:
+            outs = [torch.zeros(64, dtype=torch.float64, device="cuda") for _ in range(12)]
+            bout = torch.zeros(1 << 16, dtype=torch.float64, device="cuda")
+            for o in outs:
+                c.recv(o, peer, tag=7)
+            c.recv(bout, peer, tag=7)
+            ok = ok and all(bool((o == float(i)).all()) for i, o in enumerate(outs))
+            ok = ok and bool(torch.equal(bout, torch.arange(1 << 16, dtype=torch.float64, device="cuda")))
+        c.barrier()
+        after = cm.device_eager_stats()
+        return ok, after["eager"] - before["eager"], after["too_large"] - before["too_large"]
+    res = cm.run_local(2, body)
+    assert res[0][0] and res[1][0]
+    assert res[0][1] + res[1][1] >= 4          # counters are per process (both thread ranks)
+    assert res[0][2] + res[1][2] >= 1          # the 512 KiB message took the rendezvous
+
+
+def test_comm_device_strided_column_and_multi_buffer_hindexed_types():
+    """Derived types on DEVICE memory through send/recv: (a) a ghost column of a 2-D tile
+    (subarray, 8-byte runs at row pitch) gathered by the sender and scattered into another column
+    by the receiver; (b) the reference's nested type of mpi-complex-types.cpp:32-58 -- a 1-D
+    subarray (3 of 8 ints) wrapped in an hindexed type whose byte displacements point into THREE
+    SEPARATE allocations (signed, arbitrary distances) -- gathered from three device buffers by
+    one send and scattered into three device buffers by one receive."""
+    H = W = 256
+    def body(c):
+        torch.cuda.set_device(0)
+        peer = 1 - c.rank
+        col_send = DOUBLE.subarray([H, W], [H, 1], [0, W - 2]).commit()     # my last core column
+        col_recv = DOUBLE.subarray([H, W], [H, 1], [0, 0]).commit()         # my left ghost column
+        tile = torch.arange(H * W, dtype=torch.float64, device="cuda").reshape(H, W) + 1e6 * c.rank
+        r = c.irecv(tile, peer, tag=3, count=1, datatype=col_recv)
+        s = c.isend(tile, peer, tag=3, count=1, datatype=col_send)
+        r.wait(); s.wait()
+        want = torch.arange(H * W, dtype=torch.float64, device="cuda").reshape(H, W)[:, W - 2] + 1e6 * peer
+        ok = bool(torch.equal(tile[:, 0], want))
+        # (b) three separate allocations
+        sub_s = INT.subarray([8], [3], [3]).commit()
+        sub_r = INT.subarray([8], [3], [0]).commit()
+        bufs = [torch.full((8,), -1, dtype=torch.int32, device="cuda") for _ in range(3)]
+        pad = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")          # keeps them apart
+        disps = [0, bufs[1].data_ptr() - bufs[0].data_ptr(), bufs[2].data_ptr() - bufs[0].data_ptr()]
+        if c.rank == 0:
+            for k, b in enumerate(bufs):
+                b.copy_(torch.arange(8, dtype=torch.int32, device="cuda") * (k + 1))
+            t = sub_s.hindexed([1, 1, 1], disps).commit()
+            c.send(bufs[0], 1, tag=4, count=1, datatype=t)
+            del pad
+            return ok, None
+        t = sub_r.hindexed([1, 1, 1], disps).commit()
+        c.recv(bufs[0], 0, tag=4, count=1, datatype=t)
+        del pad
+        return ok, [b.tolist() for b in bufs]
+    res = cm.run_local(2, body)
+    assert res[0][0] and res[1][0]
+    assert res[1][1] == [[3, 4, 5, -1, -1, -1, -1, -1], [6, 8, 10, -1, -1, -1, -1, -1],
+                         [9, 12, 15, -1, -1, -1, -1, -1]]
+
+
 def test_halo_plan_exchange_on_device_tiles():
     """The reference's CUDA stencil driver (mpi-2d-stencil-subarray-cuda.cu): the tile
     lives in device memory and the subarray types are applied on the GPU."""
