@@ -28,6 +28,7 @@ import torch.distributed as dist
 
 import cuda_mpi_scratch_b200 as cms
 from cuda_mpi_scratch_b200.ops.collectives import DeviceCollectives
+from cuda_mpi_scratch_b200.utils.timing import ClockSampler
 
 
 def main() -> int:
@@ -46,18 +47,31 @@ def main() -> int:
     fails = 0
     rows = []
 
+    sampler = ClockSampler(dev).start()      # clocks of every timed loop go into its row
+    sampler.wait_first(2.0)
+    clock_log = []
+
     def timed(fn):
         for _ in range(3):
             fn()
         torch.cuda.synchronize(dev)
         world.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.window_begin()
         e0.record(stream)
         for _ in range(a.iters):
             fn()
         e1.record(stream)
         torch.cuda.synchronize(dev)
+        sampler.window_end()
+        c = sampler.pop_window_summary()
+        clock_log.append({"sm_mhz": c.get("sm_mhz"), "reasons": c.get("reasons"), "samples": c.get("samples")})
         return world.allreduce_max(e0.elapsed_time(e1) / a.iters * 1e3)   # us
+
+    def with_clocks(rec):
+        rec["clocks"] = list(clock_log)
+        clock_log.clear()
+        return rec
 
     # ---------------- allreduce: sizes x algorithms ----------------
     for lg in [3, 10, 12, 14, 16, 18, 20, 22, 24, 26, 28]:
@@ -69,6 +83,8 @@ def main() -> int:
         want = src.clone()
         dist.all_reduce(want, group=pg)
         algos = ["oneshot"] if lg < 14 else (["oneshot", "twoshot"] if lg <= 22 else ["twoshot"])
+        if coll.multicast and lg >= 10:
+            algos.append("nvls")              # reduction and fan-out inside the NVSwitch
         rec = {"op": "allreduce", "bytes": 1 << lg}
         for algo in algos:
             got = coll.allreduce(src.clone(), "sum", algo)
@@ -84,9 +100,22 @@ def main() -> int:
             rec[algo + "_ok"] = bool(ok)
         work = src.clone()
         rec["nccl_us"] = round(timed(lambda: dist.all_reduce(work, group=pg)), 2)
-        rows.append(rec)
+        rows.append(with_clocks(rec))
         if rank == 0:
             print(rec, flush=True)
+
+    # in-switch reduction of fp64 and int32 (scalar multimem operations)
+    if coll.multicast:
+        for dt in (torch.float64, torch.int32):
+            v = (torch.arange(1 << 16, device=device) % 97 + rank).to(dt)
+            want = v.clone()
+            dist.all_reduce(want, group=pg)
+            got = coll.allreduce(v.clone(), "sum", "nvls")
+            coll.check()
+            ok = bool(torch.equal(got, want))
+            fails += 0 if ok else 1
+            if rank == 0:
+                print({"op": "allreduce nvls", "dtype": str(dt), "ok": ok}, flush=True)
 
     # ---------------- data movement ----------------
     blk = 1 << 20
@@ -101,7 +130,7 @@ def main() -> int:
            "ours_us": round(timed(lambda: coll.allgather(send, recv)), 2)}
     outs = list(recv.chunk(P))
     rec["nccl_us"] = round(timed(lambda: dist.all_gather(outs, send, group=pg)), 2)
-    rows.append(rec)
+    rows.append(with_clocks(rec))
     if rank == 0:
         print(rec, flush=True)
 
@@ -111,8 +140,9 @@ def main() -> int:
     ok = bool((b == float(P - 1)).all())
     fails += 0 if ok else 1
     rec = {"op": "bcast", "bytes": blk, "ok": ok, "ours_us": round(timed(lambda: coll.bcast(b, root=0)), 2),
-           "nccl_us": round(timed(lambda: dist.broadcast(b, 0, group=pg)), 2)}
-    rows.append(rec)
+           "nccl_us": round(timed(lambda: dist.broadcast(b, 0, group=pg)), 2),
+           "multicast_store": bool(coll.multicast)}
+    rows.append(with_clocks(rec))
     if rank == 0:
         print(rec, flush=True)
 
@@ -137,7 +167,7 @@ def main() -> int:
         fails += 0 if ok else 1
     rec = {"op": "barrier", "ours_us": round(timed(lambda: coll.barrier()), 2),
            "nccl_us": round(timed(lambda: dist.barrier(group=pg)), 2)}
-    rows.append(rec)
+    rows.append(with_clocks(rec))
     if rank == 0:
         print(rec, flush=True)
 
@@ -145,8 +175,17 @@ def main() -> int:
     if rank == 0:
         print("COLLECTIVES_CHECK PASSED" if tot == 0 else f"COLLECTIVES_CHECK FAILED ({int(tot)})", flush=True)
         if a.json:
+            heap = None
+            try:
+                from cuda_mpi_scratch_b200.parallel.heap import SymmetricHeap
+                hp = SymmetricHeap._by_world.get(id(world))
+                heap = None if hp is None else dict(hp.stats, multicast=bool(coll.multicast))
+            except Exception:
+                pass
             json.dump({"n_gpus": P, "iters": a.iters, "timing": "CUDA events, max over ranks, us per call",
+                       "symmetric_heap": heap,
                        "rows": rows, "check": "PASSED" if tot == 0 else "FAILED"}, open(a.json, "w"), indent=1)
+    sampler.stop()
     world.barrier()
     coll.close()
     world.finalize()

@@ -45,6 +45,7 @@ constexpr size_t kOffReady = 0, kOffDone = 512, kOffBar = 1024, kOffData = 1536,
 constexpr int kThreads = 256;
 
 struct Ws {
+    unsigned char* mc;                // multicast mapping of the workspace (same offsets), or nullptr
     unsigned char* peer[kMaxRanks];   // every rank's workspace as mapped here
     int rank, nranks;
     size_t cap;                       // bytes of one staging half
@@ -224,6 +225,128 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(const __gri
     }
 }
 
+// ---- NVLS: the same two steps with the NVSwitch doing the arithmetic and the fan-out --------
+// multimem.ld_reduce on the MULTICAST address of IN[parity] returns the sum over all ranks' staged
+// inputs (reduced inside the switch: each element crosses my link once instead of P-1 times), and
+// multimem.st to the multicast address of OUT[parity] writes every rank's output staging with one
+// store.  Rank r still owns vectors [r*vchunk, (r+1)*vchunk): one owner per element, so all ranks
+// receive the same bits.  SUM only (what the switch implements for float / double).
+template <typename T> struct Mm;
+template <> struct Mm<float> {
+    static __device__ __forceinline__ int4 ld_reduce(const void* mc) {
+        int4 v;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+        return v;
+    }
+};
+template <> struct Mm<double> {
+    static __device__ __forceinline__ int4 ld_reduce(const void* mc) {
+        union { int4 v; double d[2]; } u;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(u.d[0]) : "l"(mc) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];"
+                     : "=d"(u.d[1]) : "l"(static_cast<const char*>(mc) + 8) : "memory");
+        return u.v;
+    }
+};
+template <> struct Mm<int> {
+    static __device__ __forceinline__ int4 ld_reduce(const void* mc) {
+        int4 v;
+        const char* p = static_cast<const char*>(mc);
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(v.x) : "l"(p) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(v.y) : "l"(p + 4) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(v.z) : "l"(p + 8) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(v.w) : "l"(p + 12) : "memory");
+        return v;
+    }
+};
+template <> struct Mm<long long> {
+    static __device__ __forceinline__ int4 ld_reduce(const void* mc) {
+        union { int4 v; unsigned long long q[2]; } u;
+        const char* p = static_cast<const char*>(mc);
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(u.q[0]) : "l"(p) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(u.q[1]) : "l"(p + 8) : "memory");
+        return u.v;
+    }
+};
+__device__ __forceinline__ void mm_st_v4(void* mc, const int4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc),
+                 "f"(__int_as_float(v.x)), "f"(__int_as_float(v.y)), "f"(__int_as_float(v.z)),
+                 "f"(__int_as_float(v.w)) : "memory");
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(const __grid_constant__ Ws w, T* out,
+                                                                  int64_t n, uint64_t epoch, int phases) {
+    const int P = w.nranks;
+    const int64_t nvec = (n * (int64_t)sizeof(T) + 15) / 16;
+    const int64_t vchunk = (nvec + P - 1) / P;
+    const int64_t lo = min(nvec, (int64_t)w.rank * vchunk), hi = min(nvec, lo + vchunk);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    __shared__ bool last;
+    if (phases & 1) {
+        if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
+    }
+    if (phases & 2) {
+        wait_all(w, kOffReady, epoch);
+        const char* mc_in = reinterpret_cast<const char*>(w.mc + kOffStaging + (epoch & 1) * w.cap);
+        char* mc_out = reinterpret_cast<char*>(w.mc + kOffStaging + 2 * w.cap + (epoch & 1) * w.cap);
+        for (int64_t v = lo + tid; v < hi; v += nthr * kVecUnroll) {
+            int4 acc[kVecUnroll];
+#pragma unroll
+            for (int k = 0; k < kVecUnroll; ++k)
+                if (v + k * nthr < hi) acc[k] = Mm<T>::ld_reduce(mc_in + (v + k * nthr) * 16);
+#pragma unroll
+            for (int k = 0; k < kVecUnroll; ++k)
+                if (v + k * nthr < hi) mm_st_v4(mc_out + (v + k * nthr) * 16, acc[k]);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            ptx::fence_acq_rel_sys();
+            unsigned int* cnt = reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffCounter);
+            last = atomicInc(cnt, gridDim.x - 1) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (last) signal_all(w, kOffDone, epoch);
+    }
+    if (phases & 4) {
+        wait_all(w, kOffDone, epoch);
+        copy_out<T>(out, reinterpret_cast<const T*>(out_half(w, w.rank, epoch)), n);
+    }
+}
+
+// bcast through the switch: the root stores its buffer ONCE to the multicast address of
+// OUT[parity]; every rank (the root included) then copies out of its own staging.
+__global__ void __launch_bounds__(kThreads) push_mc_kernel(const __grid_constant__ Ws w,
+                                                           const unsigned char* src, size_t bytes,
+                                                           uint64_t epoch) {
+    __shared__ bool last;
+    char* dst = reinterpret_cast<char*>(w.mc + kOffStaging + 2 * w.cap + (epoch & 1) * w.cap);
+    const size_t nv = (bytes + 15) / 16;                 // staging is padded: whole vectors
+    const bool al = (((uintptr_t)src) & 15) == 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (size_t)gridDim.x * blockDim.x) {
+        int4 v;
+        if (al && (i + 1) * 16 <= bytes) {
+            v = ptx::ld_nc_v4(reinterpret_cast<const int4*>(src) + i);
+        } else {
+            unsigned char tmp[16];
+            for (int b = 0; b < 16; ++b) tmp[b] = i * 16 + b < bytes ? src[i * 16 + b] : 0;
+            v = *reinterpret_cast<int4*>(tmp);
+        }
+        mm_st_v4(dst + i * 16, v);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::fence_acq_rel_sys();
+        unsigned int* cnt = reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffCounter);
+        last = atomicInc(cnt, gridDim.x - 1) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last)
+        for (int r = threadIdx.x; r < w.nranks; r += blockDim.x)
+            ptx::st_release_sys(flag_at(w, r, kOffData, w.rank), epoch);
+}
+
 // ---- push: copy `bytes` of local `src` into OUT[parity] + dst_off of the ranks in
 // `targets` (bit mask over ranks, up to 64), then publish data[my rank] there ------
 struct PushArgs {
@@ -309,6 +432,7 @@ struct Plan {
     uint64_t epoch;        // operation counter: reductions AND push-type collectives (the staging
                            // halves alternate with it, so the two families must share it)
     uint64_t bar_epoch;
+    bool use_mc_bcast;     // bcast through multimem.st when the workspace has a multicast mapping
 };
 
 static size_t elem_size(int dtype) { return dtype == 8 || dtype == 5 ? 4 : 8; }
@@ -318,10 +442,12 @@ static void launch_allreduce(Plan& p, void* out, int64_t n, int op, int root, in
                              cudaStream_t st) {
     // two-shot CTAs wait (phase 4) for a flag that needs EVERY CTA of this grid to have
     // finished phase 2: the grid must be co-resident, so stay well below capacity
-    const int per_sm = (algo == 1 && root < 0) ? 2 : 4;
+    const int per_sm = (algo >= 1 && root < 0) ? 2 : 4;
     const int64_t nvec = (n * (int64_t)sizeof(T) + 15) / 16;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + kThreads - 1) / kThreads, p.sms * per_sm));
-    if (algo == 1 && root < 0)
+    if (algo == 2 && root < 0)
+        allreduce_nvls_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, p.epoch, phases);
+    else if (algo == 1 && root < 0)
         allreduce_twoshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, p.epoch, phases);
     else
         allreduce_oneshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, root,
@@ -368,6 +494,17 @@ B2C_EXPORT int b2c_coll_create(b2c_coll** out, int rank, int nranks, void* const
 }
 B2C_EXPORT int b2c_coll_destroy(b2c_coll* h) { B2C_TRY delete h; B2C_CATCH }
 
+// `mc_base`: the multicast mapping of the workspace (SymmetricHeap block with multicast=True), or
+// NULL.  With it, algo 2 of b2c_coll_allreduce reduces inside the NVSwitch and bcast uses one
+// multicast store per vector (`mc_bcast` != 0).
+B2C_EXPORT int b2c_coll_set_multicast(b2c_coll* h, void* mc_base, int mc_bcast) {
+    B2C_TRY
+    B200_REQUIRE(h, ERR_ARG, "null handle");
+    h->p.ws.mc = static_cast<unsigned char*>(mc_base);
+    h->p.use_mc_bcast = mc_base != nullptr && mc_bcast != 0;
+    B2C_CATCH
+}
+
 // dtype: 5 int32, 6 int64, 8 float32, 9 float64.  op: 0 SUM 1 PROD 2 MAX 3 MIN.
 // algo: 0 one-shot, 1 two-shot.  root < 0: allreduce.  `in` and `out` are LOCAL
 // device pointers (they may alias).  phases: 7 = all in one call; for several
@@ -386,6 +523,9 @@ B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_
     B200_REQUIRE(bytes <= p.ws.cap, ERR_COUNT,
                  "message of " + std::to_string(bytes) + " B exceeds the collective workspace (" +
                      std::to_string(p.ws.cap) + " B)");
+    if (algo == 2)
+        B200_REQUIRE(p.ws.mc != nullptr && op == 0 && root < 0, ERR_ARG,
+                     "the in-switch (NVLS) allreduce needs a multicast-bound workspace and op SUM");
     cudaStream_t st = (cudaStream_t)stream;
     if (phases & 1) {
         p.epoch += 1;
@@ -399,7 +539,7 @@ B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_
         default: launch_allreduce<int>(p, out, count, op, root, algo, phases, st); break;
     }
     // last phase of this operation on this rank (two-shot: 4, one-shot / rooted: 2)
-    const int final_phase = (algo == 1 && root < 0) ? 4 : 2;
+    const int final_phase = (algo >= 1 && root < 0) ? 4 : 2;
     if (phases & final_phase) {
         tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
         B200_CHECK_LAUNCH();
@@ -442,7 +582,10 @@ B2C_EXPORT int b2c_coll_move(b2c_coll* h, int kind, const void* sendbuf, void* r
         if (pusher) {
             B200_REQUIRE(sendbuf != nullptr || block_bytes == 0, ERR_BUFFER, "null send buffer");
             const int grid = (int)std::max<size_t>(1, std::min<size_t>((block_bytes / 16 + kThreads - 1) / kThreads, (size_t)p.sms * 2));
-            push_kernel<<<grid, kThreads, 0, st>>>(p.ws, a, epoch);
+            if (kind == 0 && p.ws.mc != nullptr && p.use_mc_bcast)
+                push_mc_kernel<<<grid, kThreads, 0, st>>>(p.ws, a.src, block_bytes, epoch);
+            else
+                push_kernel<<<grid, kThreads, 0, st>>>(p.ws, a, epoch);
             B200_CHECK_LAUNCH();
         }
     }

@@ -131,6 +131,19 @@ _proto("b2c_ipc_open", [C.c_char_p, pvp])
 _proto("b2c_ipc_close", [vp])
 _proto("b2c_enable_peer_access", [i32, i32])
 _proto("b2c_can_access_peer", [i32, i32, pi32])
+pu64 = C.POINTER(C.c_ulonglong)
+psz = C.POINTER(C.c_size_t)
+_proto("b2c_vmm_support", [i32, pi32, pi32])
+_proto("b2c_vmm_granularity", [i32, i32, psz, psz])
+_proto("b2c_vmm_create", [sz, i32, pu64, pi32])
+_proto("b2c_vmm_import", [i32, pu64])
+_proto("b2c_vmm_map", [u64, sz, sz, i32, pvp])
+_proto("b2c_vmm_unmap", [vp, sz])
+_proto("b2c_vmm_release", [u64])
+_proto("b2c_mc_create", [i32, sz, pu64, pi32])
+_proto("b2c_mc_add_device", [u64, i32])
+_proto("b2c_mc_bind", [u64, u64, sz])
+_proto("b2c_close_fd", [i32])
 # ---- stencil
 _proto("b2c_stencil_layout", [i32, i32, i32, C.POINTER(StencilLayout)])
 _proto("b2c_stencil_create", [pvp, i32, i32, i32, i32, vp, C.POINTER(vp * 8), i32])

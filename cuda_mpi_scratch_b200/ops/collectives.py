@@ -27,6 +27,7 @@ _vp, _i32, _i64 = C.c_void_p, C.c_int, C.c_int64
 _lib._proto("b2c_coll_workspace_bytes", [C.c_size_t, C.POINTER(C.c_size_t)])
 _lib._proto("b2c_coll_create", [C.POINTER(_vp), _i32, _i32, C.POINTER(_vp), C.c_size_t])
 _lib._proto("b2c_coll_destroy", [_vp])
+_lib._proto("b2c_coll_set_multicast", [_vp, _vp, _i32])
 _lib._proto("b2c_coll_allreduce", [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp])
 _lib._proto("b2c_coll_move", [_vp, _i32, _vp, _vp, C.c_size_t, _i32, _i32, _vp])
 _lib._proto("b2c_coll_barrier", [_vp, _i32, _vp])
@@ -61,10 +62,15 @@ class DeviceCollectives:
             _lib.check(_L.b2c_coll_create(C.byref(h), rank, nranks, ws, max_bytes))
         self._h = h
         self.kernel_launches = 0
+        #: the workspace has an NVLink multicast mapping: in-switch allreduce ("nvls") and
+        #: one-store broadcast are available
+        self.multicast = bool(getattr(symbuf, "mc_ptr", 0))
+        if self.multicast:
+            _lib.check(_L.b2c_coll_set_multicast(h, C.c_void_p(symbuf.mc_ptr), 1))
 
     @classmethod
     def create(cls, world: World, max_bytes: int = 64 << 20, **kw) -> "DeviceCollectives":
-        sym = SymmetricBuffer.allocate(world, workspace_bytes(max_bytes))
+        sym = SymmetricBuffer.allocate(world, workspace_bytes(max_bytes), multicast=True)
         return cls(world.rank, world.size, sym, max_bytes, world, **kw)
 
     @classmethod
@@ -76,8 +82,11 @@ class DeviceCollectives:
     # ---- reductions ----------------------------------------------------------
     def _algo(self, t: torch.Tensor, algo: str) -> int:
         if algo == "auto":
-            return 1 if t.numel() * t.element_size() >= self.twoshot_min_bytes and self.nranks > 1 else 0
-        return {"oneshot": 0, "twoshot": 1}[algo]
+            big = t.numel() * t.element_size() >= self.twoshot_min_bytes and self.nranks > 1
+            return (2 if self.multicast and self._nvls_op else 1) if big else 0
+        if algo == "nvls" and not self.multicast:
+            raise _lib.CommError(_lib.ERR_STATE, "no multicast mapping: the in-switch allreduce is not available")
+        return {"oneshot": 0, "twoshot": 1, "nvls": 2}[algo]
 
     def allreduce(self, t: torch.Tensor, op: str = "sum", algo: str = "auto", out: torch.Tensor | None = None,
                   phases: int = 7, root: int = -1) -> torch.Tensor:
@@ -85,6 +94,7 @@ class DeviceCollectives:
         if t.dtype not in _DT or not t.is_contiguous():
             raise TypeError("need a contiguous int32/int64/float32/float64 CUDA tensor")
         out = t if out is None else out
+        self._nvls_op = op == "sum" and root < 0          # what the switch can reduce
         with torch.cuda.device(self.device):
             _lib.check(_L.b2c_coll_allreduce(self._h, t.data_ptr(), out.data_ptr(), t.numel(), _DT[t.dtype],
                                              OPS[op], root, self._algo(t, algo) if root < 0 else 0,

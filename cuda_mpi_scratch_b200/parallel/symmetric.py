@@ -57,18 +57,37 @@ class SymmetricBuffer:
     """One rank's view of a symmetric allocation."""
 
     def __init__(self, rank: int, size: int, nbytes: int, device: int, local_ptr: int,
-                 peer_ptrs: Sequence[int], opened: Sequence[int] = (), owns: bool = True):
+                 peer_ptrs: Sequence[int], opened: Sequence[int] = (), owns: bool = True,
+                 block=None):
         self.rank, self.size, self.nbytes, self.device = rank, size, nbytes, device
         self.local_ptr = int(local_ptr)
         self.peer_ptrs = [int(p) for p in peer_ptrs]
         self._opened = list(opened)
         self._owns = owns
         self._freed = False
+        self._block = block              # HeapBlock when the memory comes from the symmetric heap
+        #: multicast address of the block (0: none): a store there lands in EVERY rank's copy
+        self.mc_ptr = int(block.mc_ptr) if block is not None else 0
 
     # -- factories ---------------------------------------------------------
     @staticmethod
-    def allocate(world: World, nbytes: int) -> "SymmetricBuffer":
-        """Collective over ``world``."""
+    def allocate(world: World, nbytes: int, multicast: bool = False) -> "SymmetricBuffer":
+        """Collective over ``world``.  Multi-process worlds sub-allocate from the world's
+        :class:`~cuda_mpi_scratch_b200.parallel.heap.SymmetricHeap` (one VMM mapping per arena and
+        peer, optional NVLink multicast binding); ``B200COMM_HEAP=ipc`` or a driver without
+        exportable allocations falls back to one ``cudaMalloc`` + CUDA-IPC mapping per buffer."""
+        if world.size > 1:
+            from .heap import SymmetricHeap
+            if SymmetricHeap.enabled(world):
+                try:
+                    heap = SymmetricHeap.for_world(world)
+                except _lib.CommError:
+                    heap = None
+                # all ranks take the same path
+                if world.allreduce_max(0.0 if heap is not None else 1.0) == 0.0:
+                    blk = heap.alloc(nbytes, multicast=multicast)
+                    return SymmetricBuffer(world.rank, world.size, blk.nbytes, world.device, blk.local_ptr,
+                                           blk.peer_ptrs, (), owns=False, block=blk)
         p = C.c_void_p()
         _lib.check(_lib.lib.b2c_malloc(C.byref(p), nbytes))
         if world.size == 1:
@@ -120,6 +139,9 @@ class SymmetricBuffer:
         if self._freed:
             return
         self._freed = True
+        if self._block is not None:
+            self._block.heap.free(self._block)
+            return
         for q in self._opened:
             _lib.lib.b2c_ipc_close(C.c_void_p(q))
         if self._owns:

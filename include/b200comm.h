@@ -75,6 +75,24 @@ int b2c_ipc_close(void* ptr);
 int b2c_enable_peer_access(int device, int peer_device);
 int b2c_can_access_peer(int device, int peer_device, int* yes);
 
+/* Symmetric heap building blocks (csrc/core/vmm.cpp): physical allocations that are exported as
+ * POSIX file descriptors, imported and mapped by the peers (no cudaIpc*, one mapping per arena),
+ * and NVLink multicast objects bound to them, so that one store reaches every rank's memory and
+ * one multimem.ld_reduce returns the in-switch sum.  The Python SymmetricHeap drives these calls
+ * and moves the descriptors between processes (SCM_RIGHTS).  Reference counterpart: none -- the
+ * reference hands device pointers to a CUDA-aware MPI (stencil2d/stencil2D.h:369-373). */
+int b2c_vmm_support(int device, int* vmm, int* multicast);
+int b2c_vmm_granularity(int device, int ndevices, size_t* alloc_gran, size_t* mc_gran);
+int b2c_vmm_create(size_t bytes, int device, unsigned long long* handle, int* fd);
+int b2c_vmm_import(int fd, unsigned long long* handle);
+int b2c_vmm_map(unsigned long long handle, size_t bytes, size_t align, int device, void** ptr);
+int b2c_vmm_unmap(void* ptr, size_t bytes);
+int b2c_vmm_release(unsigned long long handle);
+int b2c_mc_create(int ndevices, size_t bytes, unsigned long long* handle, int* fd);
+int b2c_mc_add_device(unsigned long long mc, int device);
+int b2c_mc_bind(unsigned long long mc, unsigned long long mem, size_t bytes);
+int b2c_close_fd(int fd);
+
 /* -------------------------------------------------------------- datatypes */
 /* Derived datatypes.  Reference: MPI_Type_indexed (mpi7.cpp:32-41),
  * MPI_Type_create_struct + MPI_Type_extent (mpi8.cpp:38-54),
@@ -290,6 +308,11 @@ typedef struct b2c_coll b2c_coll;
 int b2c_coll_workspace_bytes(size_t max_bytes, size_t* bytes);
 int b2c_coll_create(b2c_coll** out, int rank, int nranks, void* const* workspaces, size_t max_bytes);
 int b2c_coll_destroy(b2c_coll* c);
+/* Multicast mapping of the workspace (NULL: none).  Enables algo 2 of b2c_coll_allreduce -- the
+ * sum is formed inside the NVSwitch (multimem.ld_reduce) and fanned out by it (multimem.st) -- and,
+ * with mc_bcast != 0, bcast through one multicast store per vector.  Reference capability:
+ * MPI_Allreduce mpi9.cpp:51-54, MPI_Bcast mpicuda2.cu:154 (host scalars there). */
+int b2c_coll_set_multicast(b2c_coll* c, void* mc_base, int mc_bcast);
 int b2c_coll_allreduce(b2c_coll* c, const void* in, void* out, int64_t count, int dtype, int op,
                        int root /* <0: allreduce */, int algo, int phases, void* stream);
 int b2c_coll_move(b2c_coll* c, int kind, const void* sendbuf, void* recvbuf, size_t block_bytes,
