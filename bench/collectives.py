@@ -73,6 +73,9 @@ def main() -> int:
         clock_log.clear()
         return rec
 
+    # operand of the zero-copy in-switch allreduce: ONE symmetric tensor, sliced per size
+    symm = coll.symmetric_empty(max_bytes // 4, torch.float32) if coll.multicast else None
+
     # ---------------- allreduce: sizes x algorithms ----------------
     for lg in [3, 10, 12, 14, 16, 18, 20, 22, 24, 26, 28]:
         if lg > a.max_log2:
@@ -98,6 +101,21 @@ def main() -> int:
             work = src.clone()
             rec[algo + "_us"] = round(timed(lambda: coll.allreduce(work, "sum", algo)), 2)
             rec[algo + "_ok"] = bool(ok)
+        if symm is not None:
+            sl = symm[:max(n, 1)]
+            sl.copy_(src)
+            torch.cuda.synchronize(dev); world.barrier()
+            coll.allreduce_symmetric(sl)
+            coll.check()
+            ok = torch.allclose(sl, want, rtol=1e-5, atol=1e-6)
+            ref0 = sl.clone()
+            dist.broadcast(ref0, 0, group=pg)
+            ok = ok and torch.equal(ref0, sl)
+            fails += 0 if ok else 1
+            sl.zero_()
+            torch.cuda.synchronize(dev); world.barrier()
+            rec["nvls_symmetric_us"] = round(timed(lambda: coll.allreduce_symmetric(sl)), 2)
+            rec["nvls_symmetric_ok"] = bool(ok)
         work = src.clone()
         rec["nccl_us"] = round(timed(lambda: dist.all_reduce(work, group=pg)), 2)
         rows.append(with_clocks(rec))

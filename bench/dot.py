@@ -28,6 +28,7 @@ import torch.distributed as dist
 import cuda_mpi_scratch_b200 as cms
 from cuda_mpi_scratch_b200 import _lib
 from cuda_mpi_scratch_b200.models.dot import _DT, DistributedDot
+from cuda_mpi_scratch_b200.utils.timing import ClockSampler
 
 
 def main() -> int:
@@ -49,11 +50,16 @@ def main() -> int:
     d = DistributedDot.create(world)
     out = []
 
+    sampler = ClockSampler(dev).start()
+    sampler.wait_first(2.0)
+    clocks = []
+
     def timed(fn, sync_each=False):
         for _ in range(3):
             fn()
         torch.cuda.synchronize(dev); world.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.window_begin()
         t0 = time.perf_counter()
         e0.record(stream)
         for _ in range(a.iters):
@@ -61,8 +67,19 @@ def main() -> int:
         e1.record(stream)
         torch.cuda.synchronize(dev)
         wall = (time.perf_counter() - t0) / a.iters * 1e3
+        sampler.window_end()
+        clocks.append(sampler.pop_window_summary())
         ms = e0.elapsed_time(e1) / a.iters
         return world.allreduce_max(ms), world.allreduce_max(wall)
+
+    # read-only HBM peak of THIS box: the dot product only reads, so the copy peak of
+    # MEASURED_PEAKS.json (read + write) is the wrong denominator for it
+    big = torch.empty(1 << 28, dtype=torch.float64, device=f"cuda:{dev}").fill_(1.0)      # 2 GiB
+    torch.cuda.synchronize(dev)
+    ms_r, _ = timed(lambda: big.sum())
+    read_peak = big.numel() * 8 / (ms_r * 1e-3) / 1e9
+    clocks.clear()
+    del big
 
     # ---- ours: fused, stream-ordered, no host involvement
     ms, wall = timed(lambda: d.launch(x, y))
@@ -104,14 +121,17 @@ def main() -> int:
         except Exception:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
-        for r in out:
-            r.update({"n_gpus": P, "N": N, "dtype": a.dtype,
+        for i, r in enumerate(out):
+            r.update({"n_gpus": P, "N": N, "dtype": a.dtype, "clocks": clocks[i] if i < len(clocks) else None,
+                      "read_only_hbm_gbs_measured_here": round(read_peak, 1),
+                      "fraction_of_read_only_peak": round(bytes_per_gpu / (r["ms"] * 1e-3) / 1e9 / read_peak, 4),
                       "GBps_per_gpu": round(bytes_per_gpu / (r["ms"] * 1e-3) / 1e9, 1),
                       "fraction_of_measured_hbm": round(bytes_per_gpu / (r["ms"] * 1e-3) / 1e9 / hbm, 4),
                       "ms": round(r["ms"], 5), "wall_ms": round(r["wall_ms"], 5)})
             print(json.dumps(r), flush=True)
         if a.json:
             json.dump(out, open(a.json, "w"), indent=1)
+    sampler.stop()
     world.barrier()
     d.close()
     world.finalize()

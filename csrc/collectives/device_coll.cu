@@ -315,6 +315,41 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(const __grid_c
     }
 }
 
+// In place on a SYMMETRIC tensor (allocated from a multicast arena of the heap, same offset on
+// every rank): no staging copy in, no copy out.  ready-barrier, my 1/P of the vectors reduced by the
+// switch and stored back to every rank by the switch, done-barrier.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_nvls_inplace_kernel(const __grid_constant__ Ws w,
+                                                                          unsigned char* mc_data, int64_t n,
+                                                                          uint64_t epoch) {
+    const int P = w.nranks;
+    const int64_t nvec = (n * (int64_t)sizeof(T) + 15) / 16;      // blocks are 4 KiB granular: whole vectors
+    const int64_t vchunk = (nvec + P - 1) / P;
+    const int64_t lo = min(nvec, (int64_t)w.rank * vchunk), hi = min(nvec, lo + vchunk);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    __shared__ bool last;
+    if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);      // my operand was complete at launch (stream order)
+    wait_all(w, kOffReady, epoch);
+    for (int64_t v = lo + tid; v < hi; v += nthr * kVecUnroll) {
+        int4 acc[kVecUnroll];
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v + k * nthr < hi) acc[k] = Mm<T>::ld_reduce(mc_data + (v + k * nthr) * 16);
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v + k * nthr < hi) mm_st_v4(mc_data + (v + k * nthr) * 16, acc[k]);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::fence_acq_rel_sys();
+        unsigned int* cnt = reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffCounter);
+        last = atomicInc(cnt, gridDim.x - 1) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last) signal_all(w, kOffDone, epoch);
+    wait_all(w, kOffDone, epoch);          // everybody's chunk has landed in my copy
+}
+
 // bcast through the switch: the root stores its buffer ONCE to the multicast address of
 // OUT[parity]; every rank (the root included) then copies out of its own staging.
 __global__ void __launch_bounds__(kThreads) push_mc_kernel(const __grid_constant__ Ws w,
@@ -544,6 +579,36 @@ B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_
         tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
         B200_CHECK_LAUNCH();
     }
+    B2C_CATCH
+}
+
+// In-place SUM allreduce of a symmetric tensor: `mc_data` is the MULTICAST address of the tensor
+// (SymmetricBuffer.mc_ptr + offset; the tensor sits at the same offset of a multicast arena on
+// every rank).  No staging: the switch reduces and redistributes.  The whole grid waits on
+// flags, so it is sized to be co-resident.
+B2C_EXPORT int b2c_coll_allreduce_symmetric(b2c_coll* h, void* mc_data, int64_t count, int dtype,
+                                            void* stream) {
+    B2C_TRY
+    trace::Scope ts("coll_allreduce_symmetric(enqueue)", "device", -1, -3, -1, count);
+    B200_REQUIRE(h && mc_data && count >= 0, ERR_ARG, "bad argument");
+    B200_REQUIRE(dtype == 5 || dtype == 6 || dtype == 8 || dtype == 9, ERR_TYPE,
+                 "device reductions support int32, int64, float32, float64");
+    B200_REQUIRE(((uintptr_t)mc_data & 15) == 0, ERR_BUFFER, "symmetric tensors must be 16-byte aligned");
+    Plan& p = h->p;
+    cudaStream_t st = (cudaStream_t)stream;
+    p.epoch += 1;
+    const int64_t nvec = (count * (int64_t)elem_size(dtype) + 15) / 16;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec / p.ws.nranks + kThreads - 1) / kThreads, p.sms * 2));
+    unsigned char* mc = static_cast<unsigned char*>(mc_data);
+    switch (dtype) {
+        case 9: allreduce_nvls_inplace_kernel<double><<<grid, kThreads, 0, st>>>(p.ws, mc, count, p.epoch); break;
+        case 8: allreduce_nvls_inplace_kernel<float><<<grid, kThreads, 0, st>>>(p.ws, mc, count, p.epoch); break;
+        case 6: allreduce_nvls_inplace_kernel<long long><<<grid, kThreads, 0, st>>>(p.ws, mc, count, p.epoch); break;
+        default: allreduce_nvls_inplace_kernel<int><<<grid, kThreads, 0, st>>>(p.ws, mc, count, p.epoch); break;
+    }
+    B200_CHECK_LAUNCH();
+    tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
+    B200_CHECK_LAUNCH();
     B2C_CATCH
 }
 

@@ -279,6 +279,7 @@ static void build_strip_partition(Plan& p, int strip_w, int G, bool force_run,
     for (int d = 0; d < 8; ++d) p.contrib[d] = 0;
     unsigned actmask = 0;
     for (int d = 0; d < 8; ++d) if (act(d)) actmask |= 1u << d;
+    unsigned last_pin = 0;     // set by dirs_for: edges of that segment on the physical boundary
     auto dirs_for = [&](int strip, int j0, int j1) {
         const bool w = strip == 0, e = strip == NS - 1, n = j0 == 0, s = j1 == CY;
         unsigned m = 0;
@@ -286,11 +287,14 @@ static void build_strip_partition(Plan& p, int strip_w, int G, bool force_run,
         add(n, N); add(s, S); add(w, W_); add(e, E_);
         add(n && w, NW); add(n && e, NE); add(s && w, SW); add(s && e, SE);
         for (int d = 0; d < 8; ++d) if (m >> d & 1u) p.contrib[d] += 1;
+        last_pin = (n && !act(N) ? 1u : 0u) | (s && !act(S) ? 2u : 0u) | (w && !act(W_) ? 4u : 0u) |
+                   (e && !act(E_) ? 8u : 0u);
         return m & actmask;
     };
     int rr = 0;   // round-robin cursor over CTAs
     auto give = [&](int strip, int j0, int j1) {
-        per[(size_t)rr].push_back(Segment{strip, j0, j1, dirs_for(strip, j0, j1)});
+        const unsigned dm = dirs_for(strip, j0, j1);
+        per[(size_t)rr].push_back(Segment{strip, j0, j1, dm, last_pin});
         load[(size_t)rr] += (j1 - j0) + 2;
         rr = (rr + 1) % G;
     };
@@ -321,7 +325,7 @@ static void build_strip_partition(Plan& p, int strip_w, int G, bool force_run,
             for (int si = 0; si < NSi; ++si) {
                 const int cta = b * NSi + si;
                 const int j0 = 1 + (int)((long)CYi * b / NB), j1 = 1 + (int)((long)CYi * (b + 1) / NB);
-                per[(size_t)cta].push_back(Segment{1 + si, j0, j1, 0u});
+                per[(size_t)cta].push_back(Segment{1 + si, j0, j1, 0u, 0u});
             }
     } else if (ich > 0) {
         long total = ich;
@@ -338,7 +342,7 @@ static void build_strip_partition(Plan& p, int strip_w, int G, bool force_run,
                 const int j0 = 1 + (int)(next % (CY - 2));
                 const long room = (CY - 2) - (next % (CY - 2));
                 const long n = std::min(room, endi - next);
-                per[(size_t)cta].push_back(Segment{strip, j0, j0 + (int)n, 0u});
+                per[(size_t)cta].push_back(Segment{strip, j0, j0 + (int)n, 0u, 0u});
                 next += n;
             }
         }
@@ -347,7 +351,7 @@ static void build_strip_partition(Plan& p, int strip_w, int G, bool force_run,
             const int strip = 1 + (int)(next / (CY - 2));
             const int j0 = 1 + (int)(next % (CY - 2));
             const long n = std::min<long>((CY - 2) - (next % (CY - 2)), ich - next);
-            per[(size_t)G - 1].push_back(Segment{strip, j0, j0 + (int)n, 0u});
+            per[(size_t)G - 1].push_back(Segment{strip, j0, j0 + (int)n, 0u, 0u});
             next += n;
         }
     }
@@ -723,9 +727,22 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         const int CY = (H + kChunkH - 1) / kChunkH;
         const bool eligible = R <= 3 && H >= 16 && last >= R && (H % kChunkH == 0 || H % kChunkH >= R);
         const long steps_per_cta = (long)NS2 * CY / std::max(1, prop.multiProcessorCount);
-        bool use = eligible && steps_per_cta >= 48;
+        // strong scaling at 8 GPUs (8192 x 4096 tiles, 41 chunk rows per CTA): 6192 Gcell/s with
+        // this kernel vs 5160 with the tile kernel (profiles/r2/bench_8gpu_strong*.json)
+        bool use = eligible && steps_per_cta >= 16;
         if (ae && std::string(ae) == "strip") use = eligible;   // whenever it applies, however small the tile
         if (ae && std::string(ae) == "tile") use = false;
+        // A tile on the edge of a NON-PERIODIC grid has no neighbour there: its ghost cells are
+        // boundary data, and the intermediate time levels must stay fixed beyond that edge.  Only
+        // the strip kernel implements that (Segment::pin).
+        bool boundary = false;
+        for (int d : {(int)N, (int)S, (int)W_, (int)E_}) boundary = boundary || p.nbr[d] == nullptr;
+        if (boundary) {
+            B200_REQUIRE(eligible, ERR_ARG,
+                         "temporal blocking on a non-periodic grid needs 2 or 3 time steps per sweep, a tile "
+                         "of at least 16 rows and (rows mod 4) == 0 or >= the number of steps");
+            use = true;
+        }
         if (use) {
             p.algo = 2;
             p.ts_strip_w = sw;

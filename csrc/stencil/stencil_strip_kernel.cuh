@@ -43,6 +43,9 @@ struct Segment {
     int strip;        // strip index (x0 = strip * kStripW)
     int j0, j1;       // chunks [j0, j1) are computed; chunks j0-1 .. j1 are loaded
     unsigned dirs;    // directions this segment reads ghosts of / pushes to (bit d)
+    unsigned pin;     // tile edges it touches that have NO neighbour (the physical boundary of a
+                      // non-periodic grid): 1 north, 2 south, 4 west, 8 east.  The temporally blocked
+                      // strip kernel keeps intermediate time levels fixed beyond those edges.
 };
 
 struct StripParams {

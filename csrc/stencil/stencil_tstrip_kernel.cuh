@@ -208,6 +208,8 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
             // issuing warps (ncu, profiles/README.md).
             uint64_t n = 0, freed = 0;          // rows issued / output slots handed back
             uint32_t segph = 0;
+            unsigned pend[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // signals owed per direction
+            int npend = 0;
             auto free_upto = [&](uint64_t m) {
                 for (; freed < m; ++freed) ptx::mbar_arrive(&oempty[freed % NOS]);
             };
@@ -232,15 +234,24 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                     free_upto(n);
                 }
                 if (act) {
-                    // the consumers' own peer stores (edge columns) are done ...
+                    // the consumers' own peer stores (edge columns) of this segment are done
                     ptx::mbar_wait(segdone, segph);
                     segph ^= 1u;
-                    // ... and so are my bulk copies into the neighbours' ghost rows
-                    ptx::bulk_wait<0>();
+                    for (int d = 0; d < 8; ++d) pend[d] += act >> d & 1u;
+                    npend += 1;
+                }
+                // Signal ONCE per run of boundary segments (they come first in every CTA's list),
+                // not per segment: waiting for the remote writes of a segment to complete costs an
+                // NVLink round trip during which no output row leaves the stage.  The neighbours
+                // need these signals a whole sweep later.
+                const bool next_act = s + 1 < send && SP.segs[s + 1].dirs != 0;
+                if (npend && !next_act) {
+                    ptx::bulk_wait<0>();        // my bulk copies into the neighbours' ghost rows
                     free_upto(n);
                     ptx::fence_acq_rel_sys();
                     for (int d = 0; d < 8; ++d)
-                        if (act >> d & 1u) ptx::red_add_relaxed_sys(P.peer_flag[d], 1ull);
+                        if (pend[d]) { ptx::red_add_relaxed_sys(P.peer_flag[d], (uint64_t)pend[d]); pend[d] = 0; }
+                    npend = 0;
                 }
             }
             ptx::bulk_wait<0>();      // the output stage must outlive its last bulk copies
@@ -306,9 +317,9 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
         // One input row: load it, advance every level by one row, emit output row y.
         // PH = (input row) mod 3 selects the register set of every window (compile time).  ACT:
         // the segment touches the tile edge (staging code present); RS: residual wanted.
-        auto row = [&](auto phc, auto actc, auto rsc, const double* srow, double* orow_s, int y) {
+        auto row = [&](auto phc, auto actc, auto rsc, auto pinc, const double* srow, double* orow_s, int y) {
             constexpr int PH = decltype(phc)::value;
-            constexpr bool ACT = decltype(actc)::value, RS = decltype(rsc)::value;
+            constexpr bool ACT = decltype(actc)::value, RS = decltype(rsc)::value, PIN = decltype(pinc)::value;
 #pragma unroll
             for (int m = 0; m < W0 / 2; ++m) {
                 const double2 v = *reinterpret_cast<const double2*>(srow + 2 * m);
@@ -325,6 +336,14 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                 // q+off, itself q+off+1, its east neighbour q+off+2
                 const int off = (k == 1) ? RA - LV : 0;
                 const int ncol = CPT + 2 * (LV - k);
+                // PIN: beyond an edge of the PHYSICAL domain (non-periodic grid, no neighbour) the
+                // ghost cells are boundary data, fixed in time: an intermediate level there keeps
+                // the value of the level below instead of being updated.  Row i-k of level k:
+                bool pin_row = false;
+                if (PIN && k < LV) {
+                    const int yk = y + LV - k;                         // core row of this level's new row
+                    pin_row = ((sg.pin & 1u) && yk < 0) || ((sg.pin & 2u) && yk >= P.H);
+                }
 #pragma unroll
                 for (int q = 0; q < ncol; ++q) {
                     double a = c[0] * lv[k - 1][sM][q + off + 1];
@@ -332,6 +351,11 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                     a = fma(c[2], lv[k - 1][sM][q + off + 2], a);      // east
                     a = fma(c[3], lv[k - 1][sN][q + off + 1], a);      // north
                     a = fma(c[4], lv[k - 1][sS][q + off + 1], a);      // south
+                    if (PIN && k < LV) {
+                        const int xk = x0 + c0 - (LV - k) + q;         // tile column of this value
+                        if (pin_row || ((sg.pin & 4u) && xk < 0) || ((sg.pin & 8u) && xk >= P.W))
+                            a = lv[k - 1][sM][q + off + 1];
+                    }
                     if (k < LV) {
                         lv[k < LV ? k : 0][sM][q] = a;
                     } else {
@@ -375,7 +399,7 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
         // every fourth row.
         const int i_begin = (sg.j0 - 1) * CH, i_end = (sg.j1 + 1) * CH;
         const double* base = nullptr;
-        auto step = [&](auto phc, auto actc, auto rsc, int i) {
+        auto step = [&](auto phc, auto actc, auto rsc, auto pinc, int i) {
             constexpr bool ACT = decltype(actc)::value;
             const int r = (i - i_begin) & (CH - 1);
             if ((r & (SR - 1)) == 0) {
@@ -388,7 +412,7 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
             const int y = i - LV;
             const bool valid = y >= ylo && y < yhi;        // CTA-uniform
             if (valid) ptx::mbar_wait(&oempty[os], ophase ^ 1u);
-            row(phc, actc, rsc, base + (r & (SR - 1)) * G::PITCH, ostage + (size_t)os * G::SWMAX + c0, y);
+            row(phc, actc, rsc, pinc, base + (r & (SR - 1)) * G::PITCH, ostage + (size_t)os * G::SWMAX + c0, y);
             if (valid) {
                 // my part of the output row is staged: order it before the store thread's bulk copy
                 ptx::fence_proxy_async_smem();
@@ -411,21 +435,24 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                 }
             }
         };
-        auto march = [&](auto actc, auto rsc) {
+        auto march = [&](auto actc, auto rsc, auto pinc) {
             for (int i = i_begin; i < i_end; i += 3) {
-                step(std::integral_constant<int, 0>{}, actc, rsc, i);
+                step(std::integral_constant<int, 0>{}, actc, rsc, pinc, i);
                 if (i + 1 >= i_end) break;
-                step(std::integral_constant<int, 1>{}, actc, rsc, i + 1);
+                step(std::integral_constant<int, 1>{}, actc, rsc, pinc, i + 1);
                 if (i + 2 >= i_end) break;
-                step(std::integral_constant<int, 2>{}, actc, rsc, i + 2);
+                step(std::integral_constant<int, 2>{}, actc, rsc, pinc, i + 2);
             }
         };
-        if (act) {
-            if (SP.resid) march(std::true_type{}, std::true_type{});
-            else march(std::true_type{}, std::false_type{});
+        if (sg.pin) {          // touches the physical boundary (the boundary code path copes with act == 0)
+            if (SP.resid) march(std::true_type{}, std::true_type{}, std::true_type{});
+            else march(std::true_type{}, std::false_type{}, std::true_type{});
+        } else if (act) {
+            if (SP.resid) march(std::true_type{}, std::true_type{}, std::false_type{});
+            else march(std::true_type{}, std::false_type{}, std::false_type{});
         } else {
-            if (SP.resid) march(std::false_type{}, std::true_type{});
-            else march(std::false_type{}, std::false_type{});
+            if (SP.resid) march(std::false_type{}, std::true_type{}, std::false_type{});
+            else march(std::false_type{}, std::false_type{}, std::false_type{});
         }
 
         if (act) {

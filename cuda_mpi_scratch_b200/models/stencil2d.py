@@ -50,9 +50,11 @@ def layout(W: int, H: int, radius: int) -> _lib.StencilLayout:
 def _check_temporal(radius: int, kind: str, periods, temporal: int) -> None:
     if temporal == 1:
         return
-    if temporal not in (2, 3, 4) or kind != "star" or radius != 1 or not all(bool(p) for p in periods):
-        raise ValueError("temporal blocking supports temporal=2, 3 or 4 with a radius-1 star stencil "
-                         "on a fully periodic grid")
+    if temporal not in (2, 3, 4) or kind != "star" or radius != 1:
+        raise ValueError("temporal blocking supports temporal=2, 3 or 4 with a radius-1 star stencil")
+    if temporal == 4 and not all(bool(p) for p in periods):
+        raise ValueError("4 time steps per sweep need a fully periodic grid (2 and 3 also work with "
+                         "fixed boundary values on a non-periodic one)")
 
 
 def _stream_ptr(device: int) -> int:
@@ -103,10 +105,13 @@ class Stencil2D:
                push_corners: bool = True, temporal: int = 1) -> "Stencil2D":
         """Collective over ``world``: every rank gets an ``H x W`` tile.
 
-        ``temporal=T`` with T = 2, 3 or 4 (radius-1 star on a fully periodic grid): temporal
-        blocking -- every sweep of the fused kernel advances T time steps from one read and one
-        write of the grid (ghost width T, corners exchanged), bit-identical to T single steps.
-        Any step count is accepted: a remainder is done by one partial sweep."""
+        ``temporal=T`` with T = 2, 3 or 4 (radius-1 star): temporal blocking -- every sweep of the
+        fused kernel advances T time steps from one read and one write of the grid (ghost width T,
+        corners exchanged), bit-identical to T single steps.  Any step count is accepted: a
+        remainder is done by one partial sweep.  T = 2 and 3 also run on NON-PERIODIC grids (the
+        reference's topology, ``mpi10.cpp:24-27``): ghost cells beyond the edge of the global grid
+        are boundary data -- set them in BOTH buffers (:meth:`fill`) -- and stay fixed through the
+        intermediate time levels."""
         dims = tuple(dims) if dims is not None else dims_create(world.size, 2)
         cart = CartTopology.create(dims, periods)
         if cart.size != world.size:

@@ -28,6 +28,7 @@ _lib._proto("b2c_coll_workspace_bytes", [C.c_size_t, C.POINTER(C.c_size_t)])
 _lib._proto("b2c_coll_create", [C.POINTER(_vp), _i32, _i32, C.POINTER(_vp), C.c_size_t])
 _lib._proto("b2c_coll_destroy", [_vp])
 _lib._proto("b2c_coll_set_multicast", [_vp, _vp, _i32])
+_lib._proto("b2c_coll_allreduce_symmetric", [_vp, _vp, _i64, _i32, _vp])
 _lib._proto("b2c_coll_allreduce", [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp])
 _lib._proto("b2c_coll_move", [_vp, _i32, _vp, _vp, C.c_size_t, _i32, _i32, _vp])
 _lib._proto("b2c_coll_barrier", [_vp, _i32, _vp])
@@ -82,8 +83,13 @@ class DeviceCollectives:
     # ---- reductions ----------------------------------------------------------
     def _algo(self, t: torch.Tensor, algo: str) -> int:
         if algo == "auto":
-            big = t.numel() * t.element_size() >= self.twoshot_min_bytes and self.nranks > 1
-            return (2 if self.multicast and self._nvls_op else 1) if big else 0
+            nbytes = t.numel() * t.element_size()
+            # measured (profiles/r2/collectives_{2,8}gpu.json): with 8 ranks the in-switch path wins
+            # from 1 KiB up (26 vs 31 us at 1 KiB, 80 vs 324 us at 16 MiB); with 2 ranks the switch
+            # has nothing to save and one-shot / two-shot stay ahead
+            if self.multicast and self._nvls_op and self.nranks >= 4 and nbytes >= 1024:
+                return 2
+            return 1 if nbytes >= self.twoshot_min_bytes and self.nranks > 1 else 0
         if algo == "nvls" and not self.multicast:
             raise _lib.CommError(_lib.ERR_STATE, "no multicast mapping: the in-switch allreduce is not available")
         return {"oneshot": 0, "twoshot": 1, "nvls": 2}[algo]
@@ -101,6 +107,32 @@ class DeviceCollectives:
                                              phases, _stream(self.device)))
         self.kernel_launches += 1
         return out
+
+    def symmetric_empty(self, numel: int, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+        """Collective: a tensor in a MULTICAST arena of the symmetric heap, at the same offset on
+        every rank -- the operand type of :meth:`allreduce_symmetric` (no staging copies).  Keep the
+        tensor for the life of the computation: it is freed with this handle."""
+        if self.world is None or not self.multicast:
+            raise _lib.CommError(_lib.ERR_STATE, "symmetric tensors need a multi-process world with multicast")
+        sym = SymmetricBuffer.allocate(self.world, numel * torch.empty((), dtype=dtype).element_size(), multicast=True)
+        if not sym.mc_ptr:
+            raise _lib.CommError(_lib.ERR_STATE, "the heap could not bind this block to a multicast object")
+        t = sym.tensor(0, (numel,), dtype)
+        self._symm = getattr(self, "_symm", {})
+        self._symm[t.data_ptr()] = sym
+        return t
+
+    def allreduce_symmetric(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place SUM over ranks of a tensor from :meth:`symmetric_empty` (or a leading slice of
+        it): the NVSwitch reduces and redistributes, nothing is staged."""
+        sym = getattr(self, "_symm", {}).get(t.data_ptr())
+        if sym is None or t.dtype not in _DT or not t.is_contiguous():
+            raise ValueError("allreduce_symmetric needs a (slice from the start of a) tensor made by symmetric_empty")
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_allreduce_symmetric(self._h, C.c_void_p(sym.mc_ptr), t.numel(), _DT[t.dtype],
+                                                       _stream(self.device)))
+        self.kernel_launches += 2
+        return t
 
     def reduce(self, t: torch.Tensor, root: int, op: str = "sum", out: torch.Tensor | None = None,
                phases: int = 7) -> torch.Tensor | None:

@@ -313,6 +313,9 @@ int b2c_coll_destroy(b2c_coll* c);
  * with mc_bcast != 0, bcast through one multicast store per vector.  Reference capability:
  * MPI_Allreduce mpi9.cpp:51-54, MPI_Bcast mpicuda2.cu:154 (host scalars there). */
 int b2c_coll_set_multicast(b2c_coll* c, void* mc_base, int mc_bcast);
+/* In-place SUM allreduce of a tensor that lives in a multicast arena of the symmetric heap
+ * (`mc_data` = its multicast address): no staging copies, reduction and fan-out by the switch. */
+int b2c_coll_allreduce_symmetric(b2c_coll* c, void* mc_data, int64_t count, int dtype, void* stream);
 int b2c_coll_allreduce(b2c_coll* c, const void* in, void* out, int64_t count, int dtype, int op,
                        int root /* <0: allreduce */, int algo, int phases, void* stream);
 int b2c_coll_move(b2c_coll* c, int kind, const void* sendbuf, void* recvbuf, size_t block_bytes,

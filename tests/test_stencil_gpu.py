@@ -242,11 +242,55 @@ def test_temporal_strip_kernel_graph_replay_and_odd_step_counts(monkeypatch, T):
     assert torch.equal(grp.gather_global(), plain.gather_global())
 
 
+@pytest.mark.parametrize("T", [2, 3])
+@pytest.mark.parametrize("dims,tile_hw,periods", [((2, 2), (32, 128), False), ((2, 4), (40, 504), False),
+                                                  ((1, 1), (64, 3200), False), ((3, 1), (48, 1600), False),
+                                                  ((2, 2), (36, 260), (True, False)),
+                                                  ((1, 3), (32, 384), (False, True))])
+def test_temporal_blocking_on_non_periodic_grids_keeps_the_boundary_fixed(dims, tile_hw, periods, T):
+    """The reference's own topology is NON-periodic (mpi10.cpp:24-27).  Ghost cells beyond the
+    edge of the global grid are boundary data; with T time steps per sweep the intermediate
+    levels must stay pinned there.  Same bits as single steps, and the oracle of a padded grid."""
+    n = dims[0] * dims[1]
+    steps = 3 * T + 1                                        # ends with a partial sweep
+    coeffs = [0.1, 0.2, 0.25, 0.15, 0.3]
+    H, W = dims[0] * tile_hw[0], dims[1] * tile_hw[1]
+    glob = _rand_global(H, W, seed=5)
+    runs = {}
+    for temporal in (T, 1):
+        grp = Stencil2D.create_group(cms.LocalGroup(n), tile_hw, 1, "star", dims=dims, periods=periods,
+                                     temporal=temporal)
+        for s in grp.ranks:
+            s.fill(0.0, 7.5)                                 # boundary value 7.5 in both buffers
+            s.set_coeffs(coeffs)
+        grp.scatter_global(glob)
+        grp.exchange()
+        grp.step(steps, residual=True)
+        grp.sync()
+        grp.check()
+        runs[temporal] = grp
+    got = runs[T].gather_global()
+    assert torch.equal(got, runs[1].gather_global())
+    assert runs[T].residual() == pytest.approx(runs[1].residual(), rel=1e-12)
+    # oracle: pad with the boundary value where the grid is not periodic, wrap where it is
+    per = (periods, periods) if isinstance(periods, bool) else periods
+    g = glob.clone()
+    for _ in range(steps):
+        p = torch.nn.functional.pad(g[None, None], (1, 1, 1, 1), value=7.5)[0, 0]
+        if per[0]:
+            p[0, 1:-1], p[-1, 1:-1] = g[-1], g[0]
+        if per[1]:
+            p[1:-1, 0], p[1:-1, -1] = g[:, -1], g[:, 0]
+        g = (coeffs[0] * p[1:-1, 1:-1] + coeffs[1] * p[1:-1, :-2] + coeffs[2] * p[1:-1, 2:]
+             + coeffs[3] * p[:-2, 1:-1] + coeffs[4] * p[2:, 1:-1])
+    assert torch.allclose(got, g, rtol=1e-12, atol=1e-13)
+
+
 def test_temporal_blocking_rejects_what_it_cannot_do():
     with pytest.raises(ValueError):
         Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 2, "star", dims=(1, 1), temporal=2)
     with pytest.raises(ValueError):
-        Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 1, "star", dims=(1, 1), periods=False, temporal=2)
+        Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 1, "star", dims=(1, 1), periods=False, temporal=4)
     with pytest.raises(ValueError):
         Stencil2D.create_group(cms.LocalGroup(1), (64, 256), 1, "box", dims=(1, 1), temporal=2)
 
