@@ -32,6 +32,7 @@ import cuda_mpi_scratch_b200 as cms
 from cuda_mpi_scratch_b200.ops.pack_move import typed_move
 from cuda_mpi_scratch_b200.parallel.datatype import DOUBLE, FLOAT, INT, Datatype
 from cuda_mpi_scratch_b200.parallel.symmetric import SymmetricBuffer
+from cuda_mpi_scratch_b200.utils.timing import ClockSampler
 
 
 def main() -> int:
@@ -41,8 +42,10 @@ def main() -> int:
     ap.add_argument("--json", default="")
     a = ap.parse_args()
     world = cms.init()
-    assert world.size == 2
-    rank, peer, dev = world.rank, 1 - world.rank, world.device
+    assert world.size % 2 == 0, "ranks work in pairs (r, r^1)"
+    rank, peer, dev = world.rank, world.rank ^ 1, world.device
+    sampler = ClockSampler(dev).start()
+    sampler.wait_first(2.0)
     stream = torch.cuda.current_stream(dev)
     T = a.tile
     out = []
@@ -82,11 +85,13 @@ def main() -> int:
                 fn()
             torch.cuda.synchronize(dev); world.barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            sampler.window_begin()
             e0.record(stream)
             for _ in range(a.iters):
                 fn()
             e1.record(stream)
             torch.cuda.synchronize(dev)
+            sampler.window_end()
             world.barrier()
             return world.allreduce_max(e0.elapsed_time(e1) / a.iters * 1e3)
 
@@ -100,8 +105,9 @@ def main() -> int:
                          ("contiguous copy of the same payload", contiguous)):
             us = timed(fn)
             if rank == 0:
-                rec = {"case": f"column halo g={g}", "impl": name, "payload_bytes": payload,
-                       "us": round(us, 3), "GBps": round(payload / (us * 1e-6) / 1e9, 3)}
+                rec = {"case": f"column halo g={g}", "impl": name, "payload_bytes": payload, "n_gpus": world.size,
+                       "us": round(us, 3), "GBps": round(payload / (us * 1e-6) / 1e9, 3),
+                       "clocks": sampler.pop_window_summary()}
                 out.append(rec); print(json.dumps(rec), flush=True)
         # correctness of the one-kernel path: my left ghost must hold the peer's right core columns
         tile[:, :g].fill_(-1.0)
@@ -129,11 +135,13 @@ def main() -> int:
         struct_move()
     torch.cuda.synchronize(dev); world.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.window_begin()
     e0.record(stream)
     for _ in range(50):
         struct_move()
     e1.record(stream)
     torch.cuda.synchronize(dev); world.barrier()
+    sampler.window_end()
     us = world.allreduce_max(e0.elapsed_time(e1) / 50 * 1e3)
     got = sym.tensor(nrec * 32, (nrec, 24), torch.uint8)
     peer_recs = sym.peer_tensor(peer, 0, (nrec, 32), torch.uint8)
@@ -141,10 +149,51 @@ def main() -> int:
     if rank == 0:
         rec = {"case": "struct records 4f+2i (24 B of 32 B)", "impl": "typed_move (ours, 1 kernel)",
                "payload_bytes": nrec * 24, "us": round(us, 3),
-               "GBps": round(nrec * 24 / (us * 1e-6) / 1e9, 3), "check": "PASSED" if ok else "FAILED"}
+               "GBps": round(nrec * 24 / (us * 1e-6) / 1e9, 3), "check": "PASSED" if ok else "FAILED",
+               "n_gpus": world.size, "clocks": sampler.pop_window_summary()}
+        out.append(rec); print(json.dumps(rec), flush=True)
+
+    # ---- the reference's nested type (mpi-complex-types.cpp:32-58) at scale: a 1-D subarray
+    # (3 of every 8 ints) wrapped in an hindexed type whose byte displacements point into THREE
+    # SEPARATE device allocations -> one kernel gathers from all three into the peer's dense buffer
+    nblk = 1 << 16
+    bufs = [torch.randint(0, 1 << 30, (nblk * 8,), dtype=torch.int32, device=f"cuda:{dev}") for _ in range(3)]
+    blk_t = INT.subarray([8], [3], [3]).commit().resized(0, 32).commit()        # 3 ints of each 8-int record
+    arr_t = blk_t.contiguous(nblk).commit()
+    disps = [0, bufs[1].data_ptr() - bufs[0].data_ptr(), bufs[2].data_ptr() - bufs[0].data_ptr()]
+    nest_t = arr_t.hindexed([1, 1, 1], disps).commit()
+    dense3 = Datatype.basic("byte").contiguous(3 * nblk * 12).commit()
+    symc = SymmetricBuffer.allocate(world, 3 * nblk * 12)
+
+    def complex_move():
+        typed_move(bufs[0], nest_t, symc.peer_ptr(peer), dense3, device=dev)
+    for _ in range(5):
+        complex_move()
+    torch.cuda.synchronize(dev); world.barrier()
+    sampler.window_begin()
+    e0.record(stream)
+    for _ in range(50):
+        complex_move()
+    e1.record(stream)
+    torch.cuda.synchronize(dev); world.barrier()
+    sampler.window_end()
+    us = world.allreduce_max(e0.elapsed_time(e1) / 50 * 1e3)
+    # what the peer's three buffers should have delivered into MY block
+    mine = symc.tensor(0, (3, nblk, 3), torch.int32)
+    world.barrier()
+    want = torch.stack([b.reshape(nblk, 8)[:, 3:6] for b in bufs])            # what I sent
+    got_at_peer = symc.peer_tensor(peer, 0, (3, nblk, 3), torch.int32)
+    ok = bool(torch.equal(got_at_peer, want))
+    okall = world.allreduce_sum(0.0 if ok else 1.0) == 0.0
+    if rank == 0:
+        rec = {"case": "hindexed(3 x contiguous(65536 x subarray 3-of-8 ints)) over THREE allocations",
+               "impl": "typed_move (ours, 1 kernel)", "payload_bytes": 3 * nblk * 12, "us": round(us, 3),
+               "GBps": round(3 * nblk * 12 / (us * 1e-6) / 1e9, 3), "check": "PASSED" if okall else "FAILED",
+               "n_gpus": world.size, "clocks": sampler.pop_window_summary()}
         out.append(rec); print(json.dumps(rec), flush=True)
         if a.json:
             json.dump(out, open(a.json, "w"), indent=1)
+    sampler.stop()
     world.barrier()
     world.finalize()
     return 0

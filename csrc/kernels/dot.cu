@@ -391,7 +391,10 @@ B2C_EXPORT int b2c_dot_set_timeout_ms(b2c_dot* h, unsigned long long ms) {
 // The address of the array is looked up once per device, by the first call made
 // while that device is current (cudaGetSymbolAddress; its return code is
 // checked).  That first call does more than launch work, so make it before any
-// stream capture is started.
+// stream capture is started.  The address is remembered per device ordinal for
+// the life of the process: a program that calls cudaDeviceReset() on a device
+// must not use this entry point on that device afterwards (the remembered
+// address would belong to the destroyed context).
 namespace b200 {
 namespace dot {
 
