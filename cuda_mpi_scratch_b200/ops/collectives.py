@@ -84,10 +84,12 @@ class DeviceCollectives:
     def _algo(self, t: torch.Tensor, algo: str) -> int:
         if algo == "auto":
             nbytes = t.numel() * t.element_size()
-            # measured (profiles/r2/collectives_{2,8}gpu.json): with 8 ranks the in-switch path wins
+            # measured (profiles/r2/collectives_{2,4,8}gpu.json): with 8 ranks the in-switch path wins
             # from 1 KiB up (26 vs 31 us at 1 KiB, 80 vs 324 us at 16 MiB); with 2 ranks the switch
             # has nothing to save and one-shot / two-shot stay ahead
-            if self.multicast and self._nvls_op and self.nranks >= 4 and nbytes >= 1024:
+            # (4 ranks: one-shot stays ahead up to 1 MiB, 21-28 vs 22-29 us; from 4 MiB the switch wins)
+            if self.multicast and self._nvls_op and ((self.nranks >= 8 and nbytes >= 1024) or
+                                                     (self.nranks >= 4 and nbytes >= (4 << 20))):
                 return 2
             return 1 if nbytes >= self.twoshot_min_bytes and self.nranks > 1 else 0
         if algo == "nvls" and not self.multicast:
