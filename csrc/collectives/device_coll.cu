@@ -62,15 +62,17 @@ __device__ __forceinline__ unsigned char* out_half(const Ws& w, int owner, uint6
     return w.peer[owner] + kOffStaging + 2 * w.cap + (epoch & 1) * w.cap;
 }
 
-__device__ __forceinline__ void wait_flag(const Ws& w, const uint64_t* f, uint64_t epoch) {
+// false: the flag did not arrive within the time-out (status bit 8 is set; b2c_coll_check raises).
+__device__ __forceinline__ bool wait_flag(const Ws& w, const uint64_t* f, uint64_t epoch) {
     const uint64_t t0 = ptx::globaltimer_ns();
     uint32_t spins = 0;
     while (ptx::ld_acquire_sys(f) < epoch) {
         if ((++spins & 255u) == 0 && ptx::globaltimer_ns() - t0 > w.timeout_ns) {
             atomicOr(reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffStatus), 8u);
-            break;
+            return false;
         }
     }
+    return true;
 }
 
 // Tell every rank (incl. myself) that my slot of `region` reached `epoch`.
@@ -79,9 +81,13 @@ __device__ __forceinline__ void signal_all(const Ws& w, size_t region, uint64_t 
         ptx::st_release_sys(flag_at(w, r, region, w.rank), epoch);
 }
 // Wait until every rank's slot of `region` in MY workspace reached `epoch`.
-__device__ __forceinline__ void wait_all(const Ws& w, size_t region, uint64_t epoch) {
-    if ((int)threadIdx.x < w.nranks) wait_flag(w, flag_at(w, w.rank, region, threadIdx.x), epoch);
-    __syncthreads();
+// The same answer in every thread of the CTA.  On false the callers RETURN: a kernel that lost a
+// peer neither writes its output from stale data nor signals anybody (the peers then time out as
+// well and every rank's check() reports it).  The handle is not usable after a time-out.
+__device__ __forceinline__ bool wait_all(const Ws& w, size_t region, uint64_t epoch) {
+    bool ok = true;
+    if ((int)threadIdx.x < w.nranks) ok = wait_flag(w, flag_at(w, w.rank, region, threadIdx.x), epoch);
+    return __syncthreads_and(ok) != 0;
 }
 
 template <typename T> __device__ __forceinline__ T apply(T a, T b, int op) {
@@ -160,7 +166,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __gri
     }
     if (!(phases & 2)) return;
     if (root >= 0 && w.rank != root) return;
-    wait_all(w, kOffReady, epoch);
+    if (!wait_all(w, kOffReady, epoch)) return;
     constexpr int E = 16 / (int)sizeof(T);
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
     const bool aligned = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
@@ -198,7 +204,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(const __gri
         if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
     }
     if (phases & 2) {
-        wait_all(w, kOffReady, epoch);
+        if (!wait_all(w, kOffReady, epoch)) return;
         for (int64_t v = lo + tid; v < hi; v += nthr * kVecUnroll) {
             int4 acc[kVecUnroll];
             reduce_vecs<T>(w, epoch, v, nthr, hi, op, acc);
@@ -220,7 +226,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(const __gri
         if (last) signal_all(w, kOffDone, epoch);
     }
     if (phases & 4) {
-        wait_all(w, kOffDone, epoch);
+        if (!wait_all(w, kOffDone, epoch)) return;
         copy_out<T>(out, reinterpret_cast<const T*>(out_half(w, w.rank, epoch)), n);
     }
 }
@@ -288,7 +294,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(const __grid_c
         if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
     }
     if (phases & 2) {
-        wait_all(w, kOffReady, epoch);
+        if (!wait_all(w, kOffReady, epoch)) return;
         const char* mc_in = reinterpret_cast<const char*>(w.mc + kOffStaging + (epoch & 1) * w.cap);
         char* mc_out = reinterpret_cast<char*>(w.mc + kOffStaging + 2 * w.cap + (epoch & 1) * w.cap);
         for (int64_t v = lo + tid; v < hi; v += nthr * kVecUnroll) {
@@ -310,7 +316,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(const __grid_c
         if (last) signal_all(w, kOffDone, epoch);
     }
     if (phases & 4) {
-        wait_all(w, kOffDone, epoch);
+        if (!wait_all(w, kOffDone, epoch)) return;
         copy_out<T>(out, reinterpret_cast<const T*>(out_half(w, w.rank, epoch)), n);
     }
 }
@@ -329,7 +335,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_inplace_kernel(const 
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
     __shared__ bool last;
     if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);      // my operand was complete at launch (stream order)
-    wait_all(w, kOffReady, epoch);
+    if (!wait_all(w, kOffReady, epoch)) return;
     for (int64_t v = lo + tid; v < hi; v += nthr * kVecUnroll) {
         int4 acc[kVecUnroll];
 #pragma unroll
@@ -347,7 +353,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_inplace_kernel(const 
     }
     __syncthreads();
     if (last) signal_all(w, kOffDone, epoch);
-    wait_all(w, kOffDone, epoch);          // everybody's chunk has landed in my copy
+    if (!wait_all(w, kOffDone, epoch)) return;          // everybody's chunk has landed in my copy
 }
 
 // bcast through the switch: the root stores its buffer ONCE to the multicast address of
@@ -427,9 +433,10 @@ __global__ void __launch_bounds__(kThreads) pull_local_kernel(const __grid_const
                                                               unsigned char* dst, size_t src_off,
                                                               size_t bytes, unsigned long long sources,
                                                               uint64_t epoch) {
+    bool ok = true;
     if ((int)threadIdx.x < w.nranks && (sources >> threadIdx.x & 1ull))
-        wait_flag(w, flag_at(w, w.rank, kOffData, threadIdx.x), epoch);
-    __syncthreads();
+        ok = wait_flag(w, flag_at(w, w.rank, kOffData, threadIdx.x), epoch);
+    if (!__syncthreads_and(ok)) return;       // a source never delivered: leave `dst` alone
     const unsigned char* src = out_half(w, w.rank, epoch) + src_off;
     const bool al = ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0);
     const size_t nv = al ? bytes / 16 : 0;

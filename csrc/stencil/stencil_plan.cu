@@ -225,6 +225,7 @@ struct Plan {
     // ---- temporal strip kernel (algo 2, kind 2 only): shares d_segs / d_seg_begin ----
     int ts_grid, ts_slots, ts_strip_w;
     size_t ts_smem;
+    unsigned long long* ts_stamps;   // debug bit 32: [ts_grid][4] phase stamps of the last sweep
 };
 
 // Geometry of the temporal strip kernel: 6 columns per thread, 8 consumer warps.
@@ -475,6 +476,9 @@ static void launch_ts_lv(const Plan& pl, const LaunchParams& lp, bool resid, cud
     sp.strip_w = pl.ts_strip_w;
     sp.nslots = pl.ts_slots;
     sp.resid = resid ? 1 : 0;
+    sp.stamps = pl.ts_stamps;
+    if (pl.ts_stamps)      // the producer ACCUMULATES its waits: clear per sweep
+        B200_CHECK_CUDA(cudaMemsetAsync(pl.ts_stamps, 0, (size_t)pl.ts_grid * 4 * sizeof(unsigned long long), st));
     auto k = stencil_tstrip_kernel<T, LV, kTsCpt, kTsWarps>;
     static std::atomic<bool> attr_done[64];   // per device; setting it twice is harmless
     if (!attr_done[pl.device & 63]) {
@@ -764,6 +768,8 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
             B200_CHECK_CUDA(cudaMalloc(&p.d_seg_begin, begin.size() * sizeof(int)));
             B200_CHECK_CUDA(cudaMemcpy(p.d_segs, segs.data(), segs.size() * sizeof(Segment), cudaMemcpyHostToDevice));
             B200_CHECK_CUDA(cudaMemcpy(p.d_seg_begin, begin.data(), begin.size() * sizeof(int), cudaMemcpyHostToDevice));
+            if (p.debug & 32)
+                B200_CHECK_CUDA(cudaMalloc(&p.ts_stamps, (size_t)p.ts_grid * 4 * sizeof(unsigned long long)));
         }
     }
     p.ncoef = kind == 2 ? 5 : (kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1));
@@ -787,6 +793,7 @@ B2C_EXPORT int b2c_stencil_destroy(b2c_stencil* h) {
     cudaFree(h->p.resid_partials);
     if (h->p.d_segs) cudaFree(h->p.d_segs);
     if (h->p.d_seg_begin) cudaFree(h->p.d_seg_begin);
+    if (h->p.ts_stamps) cudaFree(h->p.ts_stamps);
     delete h;
     B2C_CATCH
 }
@@ -1016,6 +1023,35 @@ B2C_EXPORT int b2c_stencil_status(b2c_stencil* h, void* stream, unsigned int* st
     B200_CHECK_CUDA(cudaMemcpyAsync(status, h->p.base + kOffStatus, sizeof(unsigned),
                                     cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    B2C_CATCH
+}
+
+// Phase timing of the LAST sweep of the temporal strip kernel (plan created with
+// B2C_STENCIL_DEBUG=32; synchronises `stream`).  All in microseconds over the CTAs of this rank:
+// out[0] mean and out[1] max time from kernel start to the end of a CTA's boundary segments,
+// out[2] mean and out[3] max CTA lifetime, out[4] mean and out[5] max time a producer warp spent
+// waiting for halo flags, out[6] first-start to last-end of the grid.
+B2C_EXPORT int b2c_stencil_phase_stats(b2c_stencil* h, void* stream, double out[7]) {
+    B2C_TRY
+    B200_REQUIRE(h && out, ERR_ARG, "null argument");
+    Plan& p = h->p;
+    B200_REQUIRE(p.ts_stamps != nullptr, ERR_STATE,
+                 "no phase stamps: create the plan with B2C_STENCIL_DEBUG=32 (temporal strip kernel only)");
+    std::vector<unsigned long long> v((size_t)p.ts_grid * 4);
+    B200_CHECK_CUDA(cudaMemcpyAsync(v.data(), p.ts_stamps, v.size() * sizeof(unsigned long long),
+                                    cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    double sb = 0, mb = 0, sl = 0, ml = 0, sw = 0, mw = 0;
+    unsigned long long t0 = ~0ull, t1 = 0;
+    for (int c = 0; c < p.ts_grid; ++c) {
+        const double b = (double)(v[4 * c + 1] - v[4 * c + 0]) * 1e-3, l = (double)(v[4 * c + 2] - v[4 * c + 0]) * 1e-3,
+                     w = (double)v[4 * c + 3] * 1e-3;
+        sb += b; sl += l; sw += w;
+        mb = std::max(mb, b); ml = std::max(ml, l); mw = std::max(mw, w);
+        t0 = std::min(t0, v[4 * c + 0]); t1 = std::max(t1, v[4 * c + 2]);
+    }
+    out[0] = sb / p.ts_grid; out[1] = mb; out[2] = sl / p.ts_grid; out[3] = ml;
+    out[4] = sw / p.ts_grid; out[5] = mw; out[6] = (double)(t1 - t0) * 1e-3;
     B2C_CATCH
 }
 

@@ -71,6 +71,10 @@ struct TsParams {
     int strip_w;              // cells per strip (a multiple of CPT, <= SWMAX)
     int nslots;               // ring depth
     int resid;                // accumulate the residual of the last level
+    // debug bit 32 (B2C_STENCIL_DEBUG): per-CTA globaltimer stamps of the LAST sweep,
+    // [cta][0] start, [1] end of the boundary segments, [2] end, [3] ns the producer spent
+    // waiting for halo flags; nullptr = off
+    unsigned long long* stamps;
 };
 
 // Dynamic shared memory: nslots ring slots, then the output stage (kTsOutSlots rows of SWMAX
@@ -133,6 +137,7 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                 const Segment sg = SP.segs[s];
                 const unsigned act = sg.dirs;
                 if (act && !(P.debug & 2)) {
+                    const uint64_t tw0 = SP.stamps ? ptx::globaltimer_ns() : 0;
                     if (lane < 8 && (act >> lane & 1u)) {      // one lane per direction
                         const uint64_t t0 = ptx::globaltimer_ns();
                         uint32_t spins = 0;
@@ -148,6 +153,8 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                     // below read them through the async proxy
                     ptx::fence_proxy_async();
                     __syncwarp();
+                    if (SP.stamps && lane == 0)
+                        SP.stamps[4 * blockIdx.x + 3] += ptx::globaltimer_ns() - tw0;
                 }
                 const int x0 = sg.strip * SP.strip_w;
                 const int sw = min(SP.strip_w, P.W - x0);
@@ -282,9 +289,15 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
 #pragma unroll
             for (int b = 0; b < W0; ++b) lv[k][a][b] = 0.0;
 
+    if (SP.stamps && tid == 0) {
+        SP.stamps[4 * blockIdx.x + 0] = ptx::globaltimer_ns();
+        SP.stamps[4 * blockIdx.x + 1] = 0;
+    }
     for (int s = sbeg; s < send; ++s) {
         const Segment sg = SP.segs[s];
         const unsigned act = sg.dirs;
+        if (SP.stamps && tid == 0 && act == 0 && SP.stamps[4 * blockIdx.x + 1] == 0)
+            SP.stamps[4 * blockIdx.x + 1] = ptx::globaltimer_ns();      // boundary segments done
         const int x0 = sg.strip * SP.strip_w;
         const int sw = min(SP.strip_w, P.W - x0);              // valid columns of this strip (even)
         const bool west = x0 == 0, east = x0 + sw == P.W;
@@ -462,6 +475,11 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
         }
     }
 
+    if (SP.stamps && tid == 0) {
+        const unsigned long long t = ptx::globaltimer_ns();
+        if (SP.stamps[4 * blockIdx.x + 1] == 0) SP.stamps[4 * blockIdx.x + 1] = t;
+        SP.stamps[4 * blockIdx.x + 2] = t;
+    }
     if (SP.resid) {
         // deterministic per-CTA partial: lanes -> warps -> thread 0
 #pragma unroll

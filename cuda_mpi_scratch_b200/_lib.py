@@ -159,6 +159,7 @@ _proto("b2c_stencil_exchange_push", [vp, vp])
 _proto("b2c_stencil_exchange_wait", [vp, vp])
 _proto("b2c_stencil_fill", [vp, i32, i32, C.c_double, vp])
 _proto("b2c_stencil_status", [vp, vp, C.POINTER(C.c_uint)])
+_proto("b2c_stencil_phase_stats", [vp, vp, C.POINTER(C.c_double)])
 
 
 def have(name: str) -> bool:

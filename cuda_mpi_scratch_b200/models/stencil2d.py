@@ -295,6 +295,16 @@ class Stencil2D:
             raise _lib.CommError(_lib.ERR_TIMEOUT, "halo flag wait timed out on the device "
                                  f"(rank {self.rank}): a neighbour did not deliver")
 
+    def phase_stats(self) -> dict:
+        """Device-side timing of the LAST sweep, per phase (temporal strip kernel; create the plan
+        with ``B2C_STENCIL_DEBUG=32`` in the environment).  Microseconds, mean / max over CTAs."""
+        out = (C.c_double * 7)()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_phase_stats(self._h, _stream_ptr(self.device), out))
+        keys = ("boundary_mean_us", "boundary_max_us", "cta_mean_us", "cta_max_us",
+                "flag_wait_mean_us", "flag_wait_max_us", "grid_span_us")
+        return dict(zip(keys, [round(float(v), 2) for v in out]))
+
     def run(self, steps: int | None = None, until: Callable[[float], bool] | None = None,
             check_every: int = 10, max_steps: int = 1 << 30) -> tuple[int, float | None]:
         """``do { exchange; compute } while (!terminate)`` -- fused.

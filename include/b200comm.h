@@ -261,6 +261,10 @@ int b2c_stencil_exchange_push(b2c_stencil* s, void* stream);
 int b2c_stencil_exchange_wait(b2c_stencil* s, void* stream);
 int b2c_stencil_fill(b2c_stencil* s, int which, int region, double value, void* stream);
 int b2c_stencil_status(b2c_stencil* s, void* stream, unsigned int* status);
+/* Per-phase device timing of the last sweep (temporal strip kernel, plan created with
+ * B2C_STENCIL_DEBUG=32): boundary phase, CTA lifetime, halo-flag waits, grid span, in microseconds
+ * (mean / max over CTAs).  Reference counterpart: the clock() brackets of mpicuda3.cu:176-179. */
+int b2c_stencil_phase_stats(b2c_stencil* s, void* stream, double out[7]);
 
 /* ------------------------------------------------- P2P copy engine / flags */
 /* Kernel-initiated put into a peer-mapped buffer + device-side epoch flags, and a
