@@ -188,6 +188,15 @@ __device__ __forceinline__ void setmaxnreg_dec() {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
 }
 
+// 16-byte shared-memory load that the compiler cannot narrow.  When only one half of a pair is
+// used, ptxas turns `*(double2*)p` into LDS.64; at a 48-byte lane pitch LDS.64 is 4-way bank
+// conflicted (ncu: 2x excessive wavefronts) while LDS.128 is conflict free.
+__device__ __forceinline__ double2 lds_v2f64(const double* p) {
+    double2 v;
+    asm volatile("ld.volatile.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
+
 // Named barrier among a subset of the CTA's threads (id 1..15; 0 is __syncthreads).
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

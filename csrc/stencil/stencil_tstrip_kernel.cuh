@@ -335,7 +335,11 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
             constexpr bool ACT = decltype(actc)::value, RS = decltype(rsc)::value, PIN = decltype(pinc)::value;
 #pragma unroll
             for (int m = 0; m < W0 / 2; ++m) {
-                const double2 v = *reinterpret_cast<const double2*>(srow + 2 * m);
+                // the outermost pairs are only half used (columns c0-LV .. c0+CPT-1+LV are needed):
+                // keep them 16-byte loads, see ptx::lds_v2f64
+                const bool half_used = (2 * m < RA - LV) || (2 * m + 1 >= W0 - (RA - LV));
+                const double2 v = half_used ? ptx::lds_v2f64(srow + 2 * m)
+                                            : *reinterpret_cast<const double2*>(srow + 2 * m);
                 lv[0][PH][2 * m] = v.x;
                 lv[0][PH][2 * m + 1] = v.y;
             }

@@ -18,7 +18,7 @@ Layout
 from . import _lib
 from ._lib import B200Error, CommError, CudaError
 from .parallel.cart import PROC_NULL, CartTopology, dims_create
-from .parallel.world import (LocalGroup, SingleWorld, TorchWorld, World, bind_device, init,
+from .parallel.world import (CommWorld, LocalGroup, SingleWorld, TorchWorld, World, bind_device, init,
                              processor_name, wtime)
 from .parallel.symmetric import SymmetricBuffer
 from .models.stencil2d import Stencil2D, StencilGroup, jacobi_coeffs, reference_step

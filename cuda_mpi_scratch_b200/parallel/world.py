@@ -172,10 +172,80 @@ class TorchWorld(World):
             self._owns_pg = False
 
 
+class CommWorld(World):
+    """One process per GPU, bootstrapped by the library's OWN communicator (``parallel/comm.py``,
+    the MPI-like API over the shared-memory fabric): what ``python -m cuda_mpi_scratch_b200.launch
+    -n N prog.py`` starts.  No ``torch.distributed`` anywhere: the symmetric heap, the fused stencil,
+    the fused dot and the device collectives get their handles, barriers and max-over-ranks from
+    ``Comm.allgather`` / ``barrier`` / ``allreduce`` -- the same calls a user of the MPI-like API
+    makes (``MPI_Init`` .. ``MPI_Allreduce``, ``mpi1.cpp:11-16``, ``mpi9.cpp:51-54``)."""
+
+    def __init__(self, comm=None, device: int | None = None):
+        import numpy as np
+        from . import comm as cm
+        self._np, self._cm = np, cm
+        self.comm = comm if comm is not None else cm.init_process()
+        self._owns = comm is None
+        self.rank, self.size = self.comm.rank, self.comm.size
+        try:
+            import torch
+            cuda = torch.cuda.is_available()
+        except ImportError:  # pragma: no cover
+            cuda = False
+        self.device = (bind_device("local_rank", self.rank) if device is None else device) if cuda else -1
+
+    def allgather_bytes(self, b: bytes) -> list[bytes]:
+        np = self._np
+        lens = np.zeros(self.size, dtype=np.int64)
+        self.comm.allgather(np.array([len(b)], dtype=np.int64), lens)
+        width = max(int(lens.max()), 1)
+        mine = np.zeros(width, dtype=np.uint8)
+        mine[:len(b)] = np.frombuffer(b, dtype=np.uint8)
+        allb = np.zeros(self.size * width, dtype=np.uint8)
+        self.comm.allgather(mine, allb)
+        return [allb[r * width: r * width + int(lens[r])].tobytes() for r in range(self.size)]
+
+    def barrier(self) -> None:
+        self.comm.barrier()
+
+    def _allreduce(self, x: float, op: int) -> float:
+        np = self._np
+        a, out = np.array([x], dtype=np.float64), np.zeros(1, dtype=np.float64)
+        self.comm.allreduce(a, out, op)
+        return float(out[0])
+
+    def allreduce_max(self, x):
+        return self._allreduce(x, self._cm.MAX)
+
+    def allreduce_sum(self, x):
+        return self._allreduce(x, self._cm.SUM)
+
+    def allreduce_max_vec(self, xs):
+        np = self._np
+        a = np.array([float(x) for x in xs], dtype=np.float64)
+        out = np.zeros_like(a)
+        if a.size:
+            self.comm.allreduce(a, out, self._cm.MAX)
+        return out.tolist()
+
+    def abort(self, code: int = 1) -> None:
+        self.comm.abort(code)
+
+    def finalize(self) -> None:
+        if self._owns:
+            self.comm.finalize()
+            self._owns = False
+
+
 def init(backend: str | None = None) -> World:
-    """``MPI_Init`` analogue: returns the world for this process."""
+    """``MPI_Init`` analogue: returns the world for this process.  Under ``torchrun``
+    (``WORLD_SIZE`` > 1): :class:`TorchWorld`; under the library's own launcher (``B200_RANK`` /
+    ``B200_WORLD_SIZE``, ``python -m cuda_mpi_scratch_b200.launch``): :class:`CommWorld`, no
+    ``torch.distributed`` involved; otherwise a world of one."""
+    if backend != "torch" and int(os.environ.get("B200_WORLD_SIZE", "1")) > 1 and "WORLD_SIZE" not in os.environ:
+        return CommWorld()
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
-        return TorchWorld(backend)
+        return TorchWorld(None if backend == "torch" else backend)
     return SingleWorld()
 
 
