@@ -326,6 +326,8 @@ def main(argv=None) -> int:
                              % (th * tw * 8 / 2 ** 30),
                        "halo": "fused: peer stores + epoch flags inside the stencil kernel",
                        "time_steps_per_kernel_sweep": T,
+                       "kernel": ("stencil_tstrip_kernel (strips marched top to bottom, time levels in registers)"
+                                  if st.info().threads == 384 else "stencil_fused_kernel (tiles)"),
                        "timing": "K-step batches, each between barrier+synchronize, CUDA events, max "
                                  "over ranks per batch, repeated for >= %.1f s; value = median batch"
                                  % args.min_seconds},

@@ -159,13 +159,30 @@ __device__ __forceinline__ void copy_out(T* out, const T* src, int64_t n) {
 template <typename T>
 __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __grid_constant__ Ws w, T* out,
                                                                      int64_t n, int op, int root,
-                                                                     uint64_t epoch, int phases) {
+                                                                     uint64_t epoch, int phases,
+                                                                     const T* fused_in) {
+    // fused_in != nullptr: SMALL message, ONE CTA, everything in this launch -- the CTA stages the
+    // operand itself (no cudaMemcpyAsync before) and does the consumed-epoch exchange itself (no
+    // tail kernel after): one launch instead of three, ~5 us less for an 8-byte allreduce.
+    if (fused_in != nullptr) {
+        unsigned char* stage = in_half(w, w.rank, epoch);
+        const int64_t nb = n * (int64_t)sizeof(T);
+        for (int64_t b = threadIdx.x; b < nb; b += blockDim.x)
+            stage[b] = reinterpret_cast<const unsigned char*>(fused_in)[b];
+        __syncthreads();
+    }
     if (phases & 1) {
-        // the input was staged by an earlier operation in this stream: publish it
+        // the input was staged by an earlier operation in this stream (or just above): publish it
         if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
     }
     if (!(phases & 2)) return;
-    if (root >= 0 && w.rank != root) return;
+    if (root >= 0 && w.rank != root) {
+        if (fused_in != nullptr) {            // folded tail (see tail_kernel)
+            signal_all(w, kOffConsumed, epoch);
+            if (epoch > 1) wait_all(w, kOffConsumed, epoch - 1);
+        }
+        return;
+    }
     if (!wait_all(w, kOffReady, epoch)) return;
     constexpr int E = 16 / (int)sizeof(T);
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
@@ -184,6 +201,11 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(const __gri
             acc = apply(acc, *reinterpret_cast<const volatile T*>(
                                  reinterpret_cast<const T*>(in_half(w, r, epoch)) + i), op);
         out[i] = acc;
+    }
+    if (fused_in != nullptr) {                // folded tail: every thread of the only CTA has read
+        __syncthreads();
+        signal_all(w, kOffConsumed, epoch);
+        if (epoch > 1) wait_all(w, kOffConsumed, epoch - 1);
     }
 }
 
@@ -354,6 +376,10 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_inplace_kernel(const 
     __syncthreads();
     if (last) signal_all(w, kOffDone, epoch);
     if (!wait_all(w, kOffDone, epoch)) return;          // everybody's chunk has landed in my copy
+    if (gridDim.x == 1) {                               // small tensor: the back-pressure tail rides along
+        signal_all(w, kOffConsumed, epoch);
+        if (epoch > 1) wait_all(w, kOffConsumed, epoch - 1);
+    }
 }
 
 // bcast through the switch: the root stores its buffer ONCE to the multicast address of
@@ -481,7 +507,7 @@ static size_t elem_size(int dtype) { return dtype == 8 || dtype == 5 ? 4 : 8; }
 
 template <typename T>
 static void launch_allreduce(Plan& p, void* out, int64_t n, int op, int root, int algo, int phases,
-                             cudaStream_t st) {
+                             cudaStream_t st, const void* fused_in) {
     // two-shot CTAs wait (phase 4) for a flag that needs EVERY CTA of this grid to have
     // finished phase 2: the grid must be co-resident, so stay well below capacity
     const int per_sm = (algo >= 1 && root < 0) ? 2 : 4;
@@ -492,8 +518,8 @@ static void launch_allreduce(Plan& p, void* out, int64_t n, int op, int root, in
     else if (algo == 1 && root < 0)
         allreduce_twoshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, p.epoch, phases);
     else
-        allreduce_oneshot_kernel<T><<<grid, kThreads, 0, st>>>(p.ws, static_cast<T*>(out), n, op, root,
-                                                               p.epoch, phases);
+        allreduce_oneshot_kernel<T><<<fused_in ? 1 : grid, kThreads, 0, st>>>(
+            p.ws, static_cast<T*>(out), n, op, root, p.epoch, phases, static_cast<const T*>(fused_in));
     B200_CHECK_LAUNCH();
 }
 
@@ -569,20 +595,26 @@ B2C_EXPORT int b2c_coll_allreduce(b2c_coll* h, const void* in, void* out, int64_
         B200_REQUIRE(p.ws.mc != nullptr && op == 0 && root < 0, ERR_ARG,
                      "the in-switch (NVLS) allreduce needs a multicast-bound workspace and op SUM");
     cudaStream_t st = (cudaStream_t)stream;
+    // small one-shot operations issued in one piece: a single launch does staging, reduction
+    // and the consumed-epoch exchange
+    const bool one_shot = !(algo >= 1 && root < 0);
+    const void* fused_in = (one_shot && (phases & 3) == 3 && bytes <= 4096) ? in : nullptr;
     if (phases & 1) {
         p.epoch += 1;
-        unsigned char* stage = p.ws.peer[p.ws.rank] + kOffStaging + (p.epoch & 1) * p.ws.cap;
-        B200_CHECK_CUDA(cudaMemcpyAsync(stage, in, bytes, cudaMemcpyDeviceToDevice, st));
+        if (!fused_in) {
+            unsigned char* stage = p.ws.peer[p.ws.rank] + kOffStaging + (p.epoch & 1) * p.ws.cap;
+            B200_CHECK_CUDA(cudaMemcpyAsync(stage, in, bytes, cudaMemcpyDeviceToDevice, st));
+        }
     }
     switch (dtype) {
-        case 9: launch_allreduce<double>(p, out, count, op, root, algo, phases, st); break;
-        case 8: launch_allreduce<float>(p, out, count, op, root, algo, phases, st); break;
-        case 6: launch_allreduce<long long>(p, out, count, op, root, algo, phases, st); break;
-        default: launch_allreduce<int>(p, out, count, op, root, algo, phases, st); break;
+        case 9: launch_allreduce<double>(p, out, count, op, root, algo, phases, st, fused_in); break;
+        case 8: launch_allreduce<float>(p, out, count, op, root, algo, phases, st, fused_in); break;
+        case 6: launch_allreduce<long long>(p, out, count, op, root, algo, phases, st, fused_in); break;
+        default: launch_allreduce<int>(p, out, count, op, root, algo, phases, st, fused_in); break;
     }
     // last phase of this operation on this rank (two-shot: 4, one-shot / rooted: 2)
     const int final_phase = (algo >= 1 && root < 0) ? 4 : 2;
-    if (phases & final_phase) {
+    if ((phases & final_phase) && !fused_in) {
         tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
         B200_CHECK_LAUNCH();
     }
@@ -614,8 +646,10 @@ B2C_EXPORT int b2c_coll_allreduce_symmetric(b2c_coll* h, void* mc_data, int64_t 
         default: allreduce_nvls_inplace_kernel<int><<<grid, kThreads, 0, st>>>(p.ws, mc, count, p.epoch); break;
     }
     B200_CHECK_LAUNCH();
-    tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
-    B200_CHECK_LAUNCH();
+    if (grid > 1) {             // (a single CTA does the consumed-epoch exchange itself)
+        tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
+        B200_CHECK_LAUNCH();
+    }
     B2C_CATCH
 }
 

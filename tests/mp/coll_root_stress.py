@@ -77,6 +77,18 @@ def main():
         if rank == root:
             want = float(sum(r + it + 1 for r in range(P)) * n)
             bad += (dot.result_tensor() != want).sum()
+        # ---- small messages take the single-launch path (staging + reduction + consumed-epoch
+        # exchange in one kernel): a rooted reduce and an allreduce of a few values
+        slow(root)
+        small = torch.arange(8, dtype=torch.float64, device=device) + float(rank * 10 + it)
+        sout = torch.empty_like(small)
+        coll.reduce(small, root, out=sout)
+        if rank == root:
+            want = torch.arange(8, dtype=torch.float64, device=device) * P + float(sum(r * 10 + it for r in range(P)))
+            bad += (sout != want).sum()
+        one = torch.full((1,), float(rank + it), dtype=torch.float32, device=device)
+        coll.allreduce(one)
+        bad += (one != float(sum(r + it for r in range(P)))).sum()
         # ---- every third round an allreduce in between (mixes the two families of operations)
         if it % 3 == 2:
             v = ones * float(rank + 1)
