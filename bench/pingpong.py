@@ -14,6 +14,7 @@ in-kernel globaltimer), and the echoed buffer is compared with the original (PAS
 paths
     kernel_ldst / kernel_tma   product: put kernel -> peer buffer + release flag, acquire kernel
     device_loop                product: whole loop inside one kernel per GPU (latency floor)
+    bidir_tma / bidir_ldst     both ranks put at the same time (GBps_one_way = per direction while BOTH run)
     copy_engine                baseline: cudaMemcpyAsync to the peer mapping + flag kernel
     nccl                       baseline: torch.distributed send/recv (NCCL)
     comm_sync / comm_async     MPI-like API on device tensors: <= 64 KiB eager through the receiver's
@@ -84,6 +85,11 @@ def main() -> int:
                 ch.wait(peer)
                 ch.put(peer, ch.recv_view(torch.float64, n), mode=mode, max_ctas=a.ctas)
 
+        def bidir_kernel(mode):
+            # both directions at once: each rank puts to the other, then waits for the other's put
+            ch.put(peer, src, mode=mode, max_ctas=a.ctas)
+            ch.wait(peer)
+
         def roundtrip_copy_engine():
             pdata = ch.symbuf.peer_ptr(peer) + _OFF_DATA
             pflag = ch.symbuf.peer_ptr(peer) + _OFF_FLAGS + 8 * rank
@@ -132,7 +138,8 @@ def main() -> int:
                 continue
             if path in ("comm_sync", "comm_async") and nbytes > 1 << 27:
                 pass
-            fn = {"kernel_ldst": lambda: roundtrip_kernel("ldst"),
+            fn = {"bidir_tma": lambda: bidir_kernel("tma"), "bidir_ldst": lambda: bidir_kernel("ldst"),
+                  "kernel_ldst": lambda: roundtrip_kernel("ldst"),
                   "kernel_tma": lambda: roundtrip_kernel("tma"),
                   "copy_engine": roundtrip_copy_engine, "nccl": roundtrip_nccl,
                   "comm_sync": lambda: roundtrip_comm(False), "comm_async": lambda: roundtrip_comm(True),
@@ -176,13 +183,15 @@ def main() -> int:
                     timer = "CUDA events on rank 0"
                 sampler.window_end()
                 if rank == 0:
-                    got = ch.recv_view(torch.float64, n) if path.startswith(("kernel", "copy")) else back
+                    got = ch.recv_view(torch.float64, n) if path.startswith(("kernel", "copy", "bidir")) else back
                     ok = bool(torch.equal(got, src))
             ch.check()
             rtt_max = world.allreduce_max(rtt_us) if path == "device_loop" else rtt_us
             if rank == 0:
+                # bidir_*: one "iteration" is ONE transfer per direction at the same time, not a round trip
+                one_way_s = rtt_max * 1e-6 if path.startswith("bidir") else rtt_max * 1e-6 / 2
                 rec = {"path": path, "bytes": nbytes, "iters": it, "rtt_us": round(rtt_max, 3),
-                       "GBps_one_way": round(nbytes / (rtt_max * 1e-6 / 2) / 1e9, 3),
+                       "GBps_one_way": round(nbytes / one_way_s / 1e9, 3),
                        "check": "PASSED" if ok else "FAILED", "timer": timer,
                        "clocks": sampler.pop_window_summary()}
                 results.append(rec)
