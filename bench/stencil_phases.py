@@ -31,11 +31,15 @@ def main() -> int:
     ap.add_argument("--tile", type=int, default=16384)
     ap.add_argument("--sweeps", type=int, default=40)
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--th", type=int, default=0, help="explicit tile height (with --tw)")
+    ap.add_argument("--tw", type=int, default=0)
     a = ap.parse_args()
     assert os.environ.get("B2C_STENCIL_DEBUG") == "32", "run with B2C_STENCIL_DEBUG=32"
     world = cms.init()
     dims = cms.dims_create(world.size, 2)
     th, tw = (a.tile, a.tile) if a.scaling == "weak" else (a.tile // dims[0], a.tile // dims[1])
+    if a.th and a.tw:
+        th, tw = a.th, a.tw
     st = Stencil2D.create(world, (th, tw), radius=1, dims=dims, periods=True, temporal=3)
     dev = st.device
     st.fill(0.0, 0.0)
