@@ -112,6 +112,9 @@ class DistributedDot:
         if self._h:
             _L.b2c_dot_destroy(self._h)
             self._h = None
+            sym = getattr(self, "symbuf", None)
+            if sym is not None:
+                sym.release_if_heap()
 
     def __del__(self):  # pragma: no cover
         try:

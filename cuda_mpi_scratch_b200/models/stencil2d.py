@@ -375,6 +375,7 @@ class Stencil2D:
         if self._h:
             _lib.lib.b2c_stencil_destroy(self._h)
             self._h = None
+            self.symbuf.release_if_heap()
 
     def __del__(self):  # pragma: no cover
         try:

@@ -181,6 +181,9 @@ class DeviceCollectives:
         if self._h:
             _L.b2c_coll_destroy(self._h)
             self._h = None
+            self.symbuf.release_if_heap()
+            for sym in getattr(self, "_symm", {}).values():
+                sym.release_if_heap()
 
 
 class CollectiveGroup:

@@ -135,6 +135,14 @@ class SymmetricBuffer:
         """Torch view of rank ``r``'s block (peer-mapped memory; debugging/tests)."""
         return as_tensor(self.peer_ptrs[r] + offset, shape, dtype, self.device, strides_bytes, self)
 
+    def release_if_heap(self) -> None:
+        """Give a heap block back (called by the plans' ``close()``).  The block is reused only
+        after EVERY rank has released it, so this is safe from finalisers and in any order; buffers
+        of the cudaMalloc / IPC fallback stay allocated until :meth:`free` or process exit, as
+        peers may still hold mappings of them."""
+        if self._block is not None:
+            self.free()
+
     def free(self) -> None:
         if self._freed:
             return
