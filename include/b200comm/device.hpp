@@ -98,7 +98,7 @@ private:
 
 // Fused 2-D stencil + halo exchange on a 2-D Cartesian communicator (dimension 0 = rows).
 // kind: Star (radius 1..4), Box (radius 1..2), or temporal blocking (`temporal` = 2..4 time
-// steps per kernel sweep of the radius-1 star; needs a fully periodic grid).
+// steps per kernel sweep of the radius-1 star; 4 needs a fully periodic grid).
 class FusedStencil {
 public:
     enum Kind { Star = 0, Box = 1 };
@@ -111,9 +111,11 @@ public:
         if (temporal != 1) {
             bool periodic = true;
             for (int p : cart.cart_periods()) periodic = periodic && p != 0;
-            if (temporal < 2 || temporal > 4 || radius != 1 || kind != Star || !periodic)
-                ::b200::fail_comm(ERR_ARG, "temporal blocking: 2..4 levels, radius-1 star, periodic grid",
-                                  __FILE__, __LINE__);
+            // 2 or 3 levels also run on non-periodic grids (ghost cells beyond the global edge are
+            // boundary data, kept fixed through the intermediate levels by the strip kernel)
+            if (temporal < 2 || temporal > 4 || radius != 1 || kind != Star || (temporal == 4 && !periodic))
+                ::b200::fail_comm(ERR_ARG, "temporal blocking: 2..4 levels of the radius-1 star; 4 levels "
+                                           "need a fully periodic grid", __FILE__, __LINE__);
         }
         const int g = radius * temporal;
         B200_DEVICE_OK(b2c_stencil_layout(W, H, g, &lay_));
@@ -277,6 +279,65 @@ private:
     void* stream_;
     SymmetricBlock block_;
     b2c_dot* h_ = nullptr;
+};
+
+// Collectives on DEVICE buffers over a SymmetricBlock workspace: allreduce (one-shot for small
+// messages -- a single launch up to 4 KiB -- two-shot for large ones), reduce, bcast, gather,
+// allgather, scatter, barrier; all stream-ordered kernels with epoch flags, no host in the data
+// path.  Reference capability: MPI_Allreduce mpi9.cpp:51-54, MPI_Reduce mpicuda4.cu:368, MPI_Bcast
+// mpicuda2.cu:154, MPI_Gather mpi6.cpp:89-100 -- on host scalars there.  (The in-switch variants
+// need a multicast arena of the Python SymmetricHeap; see cuda_mpi_scratch_b200.ops.collectives.)
+class DeviceCollectives {
+public:
+    enum Op { Sum = 0, Prod = 1, Max = 2, Min = 3 };
+    enum Type { Int32 = 5, Int64 = 6, Float32 = 8, Float64 = 9 };
+
+    DeviceCollectives(const comm::Comm& c, size_t max_bytes, void* stream = nullptr)
+        : comm_(c), stream_(stream), max_bytes_(max_bytes) {
+        size_t bytes = 0;
+        B200_DEVICE_OK(b2c_coll_workspace_bytes(max_bytes, &bytes));
+        block_ = SymmetricBlock(c, bytes);
+        std::vector<void*> ws((size_t)c.size());
+        for (int r = 0; r < c.size(); ++r) ws[(size_t)r] = block_.peer(r);
+        B200_DEVICE_OK(b2c_coll_create(&h_, c.rank(), c.size(), ws.data(), max_bytes));
+    }
+    DeviceCollectives(const DeviceCollectives&) = delete;
+    DeviceCollectives& operator=(const DeviceCollectives&) = delete;
+    ~DeviceCollectives() {
+        if (h_) {
+            b2c_stream_synchronize(stream_);
+            b2c_coll_destroy(h_);
+        }
+    }
+    // in == out allowed.  Large messages (>= 512 KiB) take the two-shot algorithm.
+    void allreduce(const void* in, void* out, int64_t count, Type t, Op op = Sum) {
+        const size_t esz = (t == Int32 || t == Float32) ? 4 : 8;
+        const int algo = (size_t)count * esz >= (512u << 10) && comm_.size() > 1 ? 1 : 0;
+        B200_DEVICE_OK(b2c_coll_allreduce(h_, in, out, count, (int)t, (int)op, -1, algo, 7, stream_));
+    }
+    void reduce(const void* in, void* out, int64_t count, Type t, int root, Op op = Sum) {
+        B200_DEVICE_OK(b2c_coll_allreduce(h_, in, out, count, (int)t, (int)op, root, 0, 7, stream_));
+    }
+    void bcast(void* buf, size_t bytes, int root) { B200_DEVICE_OK(b2c_coll_move(h_, 0, buf, buf, bytes, root, 3, stream_)); }
+    void gather(const void* send, void* recv, size_t block_bytes, int root) {
+        B200_DEVICE_OK(b2c_coll_move(h_, 1, send, recv, block_bytes, root, 3, stream_));
+    }
+    void allgather(const void* send, void* recv, size_t block_bytes) {
+        B200_DEVICE_OK(b2c_coll_move(h_, 2, send, recv, block_bytes, 0, 3, stream_));
+    }
+    void scatter(const void* send, void* recv, size_t block_bytes, int root) {
+        B200_DEVICE_OK(b2c_coll_move(h_, 3, send, recv, block_bytes, root, 3, stream_));
+    }
+    void barrier() { B200_DEVICE_OK(b2c_coll_barrier(h_, 3, stream_)); }
+    // synchronises the stream; throws if a peer never arrived (device-side time-out)
+    void check() { B200_DEVICE_OK(b2c_coll_check(h_, stream_)); }
+
+private:
+    comm::Comm comm_;
+    void* stream_;
+    size_t max_bytes_;
+    SymmetricBlock block_;
+    b2c_coll* h_ = nullptr;
 };
 
 }  // namespace device

@@ -33,7 +33,8 @@ def _launch(n, exe, *args, timeout=240):
                           capture_output=True, text=True)
 
 
-@pytest.mark.parametrize("name", ["halo_exchange_gpu", "pingpong_gpu", "dot_gpu", "stencil_fused_gpu"])
+@pytest.mark.parametrize("name", ["halo_exchange_gpu", "pingpong_gpu", "dot_gpu", "stencil_fused_gpu",
+                                  "collectives_gpu"])
 def test_gpu_drivers_compile_without_a_gpu(name, tmp_path):
     """The GPU drivers (the reference's CUDA main() programs) build against include/ + the library;
     without arguments the ping-pong prints its usage and exits 1 instead of reading a null argv."""
@@ -145,3 +146,13 @@ def test_mpi_shim_close_relatives(tmp_path):
                     f"-Wl,-rpath,{LIBDIR}", "-pthread"], check=True, timeout=300)
     p = _launch(4, exe, timeout=120)
     assert p.returncode == 0 and "SHIM_EXTRA PASSED" in p.stdout, p.stdout + p.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_device_collectives_driver(tmp_path):
+    """examples/cpp/collectives_gpu.cpp (b200::device::DeviceCollectives): with one visible GPU the
+    two ranks share it and the driver says so and skips (kernels of two ranks on one GPU must not
+    wait for each other); with two or more GPUs it must print PASSED."""
+    exe = _build("collectives_gpu", tmp_path)
+    p = _launch(2, exe)
+    assert p.returncode == 0 and ("PASSED" in p.stdout or "skipped" in p.stdout), p.stdout + p.stderr
