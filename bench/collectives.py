@@ -77,10 +77,12 @@ def main() -> int:
     symm = coll.symmetric_empty(max_bytes // 4, torch.float32) if coll.multicast else None
 
     # ---------------- allreduce: sizes x algorithms ----------------
-    for lg in [3, 10, 12, 14, 16, 18, 20, 22, 24, 26, 28]:
+    for lg in [3, 10, 12, 14, 16, 18, 20, 22, 24, 26, 28, 30]:
         if lg > a.max_log2:
             continue
         n = (1 << lg) // 4
+        if lg >= 30 and a.iters > 5:
+            a.iters = 5                       # 1 GiB: a few iterations are enough and keep the run short
         g = torch.Generator(device=device).manual_seed(100 + rank)
         src = torch.rand(max(n, 1), dtype=torch.float32, device=device, generator=g)
         want = src.clone()
