@@ -193,24 +193,19 @@ def main(argv=None) -> int:
     coef_host = torch.tensor(coeffs, dtype=torch.float64).pin_memory()
     h2d, d2h = coef_host.numel() * 8, 8
     chunks = [T] * (K // T) + ([K % T] if K % T else [])
-    evs = [torch.cuda.Event(), torch.cuda.Event()]
     last_res = [0.0]
 
     def e2e_batch():
         pend = None
         for i, nsub in enumerate(chunks):        # exactly K time steps, one sweep per iteration
-            s = i & 1
-            st.set_coeffs(coef_host)
-            # ghost cells of the user-visible tile are only needed when the batch ends
-            st.step(nsub, residual=True, drain=(i == len(chunks) - 1))
-            buf = st.local_residual_async(s)
-            evs[s].record(stream)
+            # Stencil2D.step_io: H2D of this sweep's coefficients (pinned) and D2H of its residual
+            # on the plan's copy streams; ghost cells of the user-visible tile are only needed
+            # when the batch ends
+            t = st.step_io(nsub, coef_host, residual=True, drain=(i == len(chunks) - 1))
             if pend is not None:
-                evs[pend[0]].synchronize()
-                last_res[0] = float(pend[1].item())
-            pend = (s, buf)
-        evs[pend[0]].synchronize()
-        last_res[0] = float(pend[1].item())
+                last_res[0] = st.wait_io(pend)   # blocks until the PREVIOUS sweep's residual is on the host
+            pend = t
+        last_res[0] = st.wait_io(pend)
 
     for _ in range(2):
         e2e_batch()
@@ -347,10 +342,11 @@ def main(argv=None) -> int:
                     "d2h_bytes_per_step": round(d2h * nsweeps / K, 3),
                     "vs_unfused_baseline": None if unf is None else
                         round(rate(e2e_stats["median"]) / unf["value"], 3),
-                    "what": f"Stencil2D.set_coeffs(pinned) + step({T}, residual=True) + residual "
-                            "D2H into pinned memory + host read (one sweep late, next sweep already "
-                            "queued), every kernel sweep; wall clock per K-step batch, max over "
-                            "ranks, median batch",
+                    "what": f"Stencil2D.step_io({T}, coeffs, residual=True) + wait_io(previous call) "
+                            "every kernel sweep: H2D of the sweep's coefficients from pinned memory "
+                            "and D2H of its residual into pinned memory on the plan's copy streams, "
+                            "host reads the residual one sweep late (next sweep already queued); "
+                            "wall clock per K-step batch, max over ranks, median batch",
                     "last_residual_sumsq": last_res[0]},
             "gpu_launches": launches,
             "launches_note": "kernels of ONE timed K-step batch, counted by the native plan: 1 fused "

@@ -36,7 +36,8 @@ constexpr size_t kOffStepFlags = 0;     // 8 x u64: fused-step epoch counters
 constexpr size_t kOffXchgFlags = 64;    // 8 x u64: unfused-exchange epoch counters
 constexpr size_t kOffStatus = 128;      // u32 status word
 constexpr size_t kOffStepCtr = 192;     // u64: fused steps completed (device-side mirror)
-constexpr size_t kOffResid = 256;       // double: last local residual (sum of squares)
+constexpr size_t kOffResid = 256;       // 3 doubles: last local residual (sum of squares) of a plain
+                                        // step, then the two slots of the pipelined step_io path
 constexpr size_t kOffRedSlots = 1024;   // scalar allreduce slots (see collectives)
 
 constexpr int kLead = 16;  // core starts 128 B into each padded row
@@ -191,6 +192,21 @@ static EncodeTiledFn get_encode_tiled() {
     return fn;
 }
 
+// Pipelined stepping (b2c_stencil_step_io): the coefficients of a sweep arrive from pinned host
+// memory and its residual leaves to pinned host memory on two copy streams of the plan, so that
+// the launching stream carries nothing but the sweep kernels.  Everything is double buffered:
+// slot i & 1 belongs to call i, and call i + 2 waits (events) for call i to have let go of it.
+struct IoState {
+    cudaStream_t h2d = nullptr, d2h = nullptr;
+    cudaEvent_t coef_ready[2] = {nullptr, nullptr};    // H2D of a coefficient slot has completed
+    cudaEvent_t coef_free[2] = {nullptr, nullptr};     // every kernel that read the slot has finished
+    cudaEvent_t sweep_done[2] = {nullptr, nullptr};    // residual slot written
+    cudaEvent_t resid_copied[2] = {nullptr, nullptr};  // residual slot in host memory
+    double* coef_stage = nullptr;    // pinned, 2 x 128
+    double* resid_stage = nullptr;   // pinned, 2
+    unsigned long long seq = 0;      // calls so far = next ticket
+};
+
 struct Plan {
     Layout L;
     int kind;          // 0 star, 1 box, 2 radius-1 star applied twice per sweep (L.R == 2)
@@ -199,9 +215,12 @@ struct Plan {
     unsigned char* base;         // my symmetric block
     unsigned char* nbr[8];       // neighbours' symmetric blocks (peer mapped) or nullptr
     CUtensorMap tmap[2];
-    double* coef_dev;
+    double* coef_dev;            // 2 x 128 doubles: two coefficient slots (see IoState)
+    double* coef_cur;            // the slot the kernels read
     int ncoef;
-    double* resid_partials;
+    double* resid_partials;      // one partial per CTA, then the tail ticket of the temporal strip kernel
+    unsigned* tail_ticket;
+    struct IoState* io;          // pipelined step_io path, created on first use
     uint64_t steps_done;         // fused steps completed since creation
     uint64_t xchg_done;          // unfused exchanges completed
     int cur;                     // index of the buffer holding the current state
@@ -226,6 +245,8 @@ struct Plan {
     int ts_grid, ts_slots, ts_strip_w;
     size_t ts_smem;
     unsigned long long* ts_stamps;   // debug bit 32: [ts_grid][4] phase stamps of the last sweep
+    double* tail_resid_out;          // per launch: where the folded tail puts the residual
+    unsigned long long tail_bump;    // per launch: step-counter increment done by the last CTA
 };
 
 // Geometry of the temporal strip kernel: 6 columns per thread, 8 consumer warps.
@@ -477,6 +498,10 @@ static void launch_ts_lv(const Plan& pl, const LaunchParams& lp, bool resid, cud
     sp.nslots = pl.ts_slots;
     sp.resid = resid ? 1 : 0;
     sp.stamps = pl.ts_stamps;
+    sp.tail_ticket = (resid || pl.tail_bump) ? pl.tail_ticket : nullptr;
+    sp.resid_out = pl.tail_resid_out;
+    sp.ctr_w = reinterpret_cast<unsigned long long*>(pl.base + kOffStepCtr);
+    sp.bump = pl.tail_bump;
     if (pl.ts_stamps)      // the producer ACCUMULATES its waits: clear per sweep
         B200_CHECK_CUDA(cudaMemsetAsync(pl.ts_stamps, 0, (size_t)pl.ts_grid * 4 * sizeof(unsigned long long), st));
     auto k = stencil_tstrip_kernel<T, LV, kTsCpt, kTsWarps>;
@@ -773,9 +798,14 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
         }
     }
     p.ncoef = kind == 2 ? 5 : (kind == 0 ? 4 * R + 1 : (2 * R + 1) * (2 * R + 1));
-    B200_CHECK_CUDA(cudaMalloc(&p.coef_dev, 128 * sizeof(double)));
-    B200_CHECK_CUDA(cudaMalloc(&p.resid_partials,
-                               (size_t)std::max(std::max(p.grid, p.strip_grid), p.ts_grid) * sizeof(double)));
+    B200_CHECK_CUDA(cudaMalloc(&p.coef_dev, 2 * 128 * sizeof(double)));
+    p.coef_cur = p.coef_dev;
+    {
+        const size_t np = (size_t)std::max(std::max(p.grid, p.strip_grid), p.ts_grid);
+        B200_CHECK_CUDA(cudaMalloc(&p.resid_partials, (np + 1) * sizeof(double)));
+        B200_CHECK_CUDA(cudaMemset(p.resid_partials, 0, (np + 1) * sizeof(double)));
+        p.tail_ticket = reinterpret_cast<unsigned*>(p.resid_partials + np);
+    }
     // default: Jacobi average of the 4R (or (2R+1)^2-1) neighbours
     double hc[128] = {0};
     const int nn = p.ncoef - 1;
@@ -789,6 +819,19 @@ B2C_EXPORT int b2c_stencil_create(b2c_stencil** out, int W, int H, int R, int ki
 B2C_EXPORT int b2c_stencil_destroy(b2c_stencil* h) {
     B2C_TRY
     if (!h) return 0;
+    if (IoState* io = h->p.io) {
+        cudaStreamSynchronize(io->h2d);
+        cudaStreamSynchronize(io->d2h);
+        for (int i = 0; i < 2; ++i) {
+            cudaEventDestroy(io->coef_ready[i]); cudaEventDestroy(io->coef_free[i]);
+            cudaEventDestroy(io->sweep_done[i]); cudaEventDestroy(io->resid_copied[i]);
+        }
+        cudaStreamDestroy(io->h2d);
+        cudaStreamDestroy(io->d2h);
+        cudaFreeHost(io->coef_stage);
+        cudaFreeHost(io->resid_stage);
+        delete io;
+    }
     cudaFree(h->p.coef_dev);
     cudaFree(h->p.resid_partials);
     if (h->p.d_segs) cudaFree(h->p.d_segs);
@@ -803,7 +846,7 @@ B2C_EXPORT int b2c_stencil_set_coef(b2c_stencil* h, const double* host_coef, int
     B200_REQUIRE(h && host_coef, ERR_ARG, "null argument");
     B200_REQUIRE(n == h->p.ncoef, ERR_COUNT,
                  "coefficient count must be " + std::to_string(h->p.ncoef));
-    B200_CHECK_CUDA(cudaMemcpyAsync(h->p.coef_dev, host_coef, sizeof(double) * n,
+    B200_CHECK_CUDA(cudaMemcpyAsync(h->p.coef_cur, host_coef, sizeof(double) * n,
                                     cudaMemcpyHostToDevice, (cudaStream_t)stream));
     B2C_CATCH
 }
@@ -871,18 +914,16 @@ static int drain_impl(Plan& p, bool xchg, cudaStream_t st) {
 // step into the pad, bit1 = append the drain (wait until the neighbours' halo
 // pushes of the last step have landed, so ghosts of the current buffer are
 // complete when the stream is synchronised).
-B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* stream) {
-    B2C_TRY
-    trace::Scope ts("stencil_step(enqueue)", "device", -1, -3, nsteps);
-    B200_REQUIRE(h && nsteps >= 0, ERR_ARG, "bad argument");
-    Plan& p = h->p;
-    cudaStream_t st = (cudaStream_t)stream;
+static void step_impl(Plan& p, int nsteps, int flags, cudaStream_t st, double* resid_out) {
+    // The temporal strip kernel does the tail of a sweep itself (last CTA: residual sum, step
+    // counter); the other kernels get one small kernel for each.
+    const bool fold = p.algo == 2;
     for (int s = 0; s < nsteps; ++s) {
         LaunchParams lp{};
         const int in = p.cur, outb = p.cur ^ 1;
         lp.in = reinterpret_cast<const double*>(p.base + p.L.off_x[in]);
         lp.out = reinterpret_cast<double*>(p.base + p.L.off_x[outb]);
-        lp.coef = p.coef_dev;
+        lp.coef = p.coef_cur;
         lp.my_flags = reinterpret_cast<const uint64_t*>(p.base + kOffStepFlags);
         lp.status = reinterpret_cast<unsigned*>(p.base + kOffStatus);
         lp.timeout_ns = p.timeout_ns;
@@ -912,23 +953,118 @@ B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* str
         lp.tilesX = p.tilesX; lp.tilesY = p.tilesY; lp.push_corners = p.push_corners;
         lp.debug = p.debug;
         const bool resid = (flags & 1) && s == nsteps - 1;
+        p.tail_resid_out = resid_out;
+        p.tail_bump = (fold && s == nsteps - 1) ? (unsigned long long)nsteps : 0ull;
         launch_step(p, lp, resid, st);
-        p.launches += resid ? 2 : 1;
-        if (resid) {
+        p.launches += (resid && !fold) ? 2 : 1;
+        if (resid && !fold) {
             sum_partials_kernel<<<1, 256, 0, st>>>(p.resid_partials,
-                                                   p.algo == 2 ? p.ts_grid : (p.algo == 1 ? p.strip_grid : p.grid),
-                                                   reinterpret_cast<double*>(p.base + kOffResid));
+                                                   p.algo == 1 ? p.strip_grid : p.grid, resid_out);
             B200_CHECK_LAUNCH();
         }
         p.cur = outb;
     }
     if (nsteps > 0) {
-        step_bump_kernel<<<1, 1, 0, st>>>(reinterpret_cast<uint64_t*>(p.base + kOffStepCtr), (uint64_t)nsteps);
-        B200_CHECK_LAUNCH();
+        if (!fold) {
+            step_bump_kernel<<<1, 1, 0, st>>>(reinterpret_cast<uint64_t*>(p.base + kOffStepCtr), (uint64_t)nsteps);
+            B200_CHECK_LAUNCH();
+            p.launches += 1;
+        }
         p.steps_done += (uint64_t)nsteps;
-        p.launches += 1;
     }
     if (flags & 2) p.launches += drain_impl(p, false, st);
+}
+
+B2C_EXPORT int b2c_stencil_step(b2c_stencil* h, int nsteps, int flags, void* stream) {
+    B2C_TRY
+    trace::Scope ts("stencil_step(enqueue)", "device", -1, -3, nsteps);
+    B200_REQUIRE(h && nsteps >= 0, ERR_ARG, "bad argument");
+    step_impl(h->p, nsteps, flags, (cudaStream_t)stream, reinterpret_cast<double*>(h->p.base + kOffResid));
+    B2C_CATCH
+}
+
+static IoState& ensure_io(Plan& p) {
+    if (p.io) return *p.io;
+    IoState* io = new IoState();
+    B200_CHECK_CUDA(cudaStreamCreateWithFlags(&io->h2d, cudaStreamNonBlocking));
+    B200_CHECK_CUDA(cudaStreamCreateWithFlags(&io->d2h, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        B200_CHECK_CUDA(cudaEventCreateWithFlags(&io->coef_ready[i], cudaEventDisableTiming));
+        B200_CHECK_CUDA(cudaEventCreateWithFlags(&io->coef_free[i], cudaEventDisableTiming));
+        B200_CHECK_CUDA(cudaEventCreateWithFlags(&io->sweep_done[i], cudaEventDisableTiming));
+        B200_CHECK_CUDA(cudaEventCreateWithFlags(&io->resid_copied[i], cudaEventDisableTiming));
+    }
+    B200_CHECK_CUDA(cudaMallocHost(&io->coef_stage, 2 * 128 * sizeof(double)));
+    B200_CHECK_CUDA(cudaMallocHost(&io->resid_stage, 2 * sizeof(double)));
+    io->resid_stage[0] = io->resid_stage[1] = 0.0;
+    p.io = io;
+    return *io;
+}
+
+// One call of a pipelined loop: `nsteps` time steps whose coefficients come from host memory and
+// whose residual (flags bit0) goes back to host memory, with both copies on the plan's own copy
+// streams -- the H2D of call i+1 and the D2H of call i-1 run while the kernels of call i do, and
+// `stream` carries the kernels only.  host_coef may be any host memory (it is staged through
+// pinned slots of the plan) or NULL (coefficients unchanged).  *ticket identifies the call for
+// b2c_stencil_io_wait; results of the last TWO calls are kept.
+B2C_EXPORT int b2c_stencil_step_io(b2c_stencil* h, int nsteps, int flags, const double* host_coef, int n,
+                                   void* stream, unsigned long long* ticket) {
+    B2C_TRY
+    B200_REQUIRE(h && nsteps >= 1 && ticket, ERR_ARG, "bad argument");
+    Plan& p = h->p;
+    IoState& io = ensure_io(p);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (host_coef) {
+        B200_REQUIRE(n == p.ncoef, ERR_COUNT, "coefficient count must be " + std::to_string(p.ncoef));
+        const int cur = p.coef_cur == p.coef_dev ? 0 : 1, tgt = cur ^ 1;
+        // staging slot tgt: its previous H2D (two switches ago) has long completed
+        B200_CHECK_CUDA(cudaEventSynchronize(io.coef_ready[tgt]));
+        std::memcpy(io.coef_stage + 128 * tgt, host_coef, sizeof(double) * n);
+        // device slot tgt: free once the kernels that read it (before the last switch) are done
+        B200_CHECK_CUDA(cudaStreamWaitEvent(io.h2d, io.coef_free[tgt], 0));
+        B200_CHECK_CUDA(cudaMemcpyAsync(p.coef_dev + 128 * tgt, io.coef_stage + 128 * tgt, sizeof(double) * n,
+                                        cudaMemcpyHostToDevice, io.h2d));
+        B200_CHECK_CUDA(cudaEventRecord(io.coef_ready[tgt], io.h2d));
+        // everything queued so far reads slot cur
+        B200_CHECK_CUDA(cudaEventRecord(io.coef_free[cur], st));
+        B200_CHECK_CUDA(cudaStreamWaitEvent(st, io.coef_ready[tgt], 0));
+        p.coef_cur = p.coef_dev + 128 * tgt;
+    }
+    const int rs = (int)(io.seq & 1);
+    double* rdev = reinterpret_cast<double*>(p.base + kOffResid) + 1 + rs;
+    // the residual slot is rewritten by this call: its copy-out of two calls ago must be over
+    B200_CHECK_CUDA(cudaStreamWaitEvent(st, io.resid_copied[rs], 0));
+    const int T = p.kind == 2 ? p.L.R : 1;
+    const int full = nsteps / T, rem = nsteps % T;
+    if (T == 1) {
+        step_impl(p, nsteps, flags, st, rdev);
+    } else {
+        if (full) step_impl(p, full, rem ? 0 : flags, st, rdev);
+        if (rem) {
+            p.partial_levels = rem;
+            step_impl(p, 1, flags, st, rdev);
+            p.partial_levels = 0;
+        }
+    }
+    B200_CHECK_CUDA(cudaEventRecord(io.sweep_done[rs], st));
+    B200_CHECK_CUDA(cudaStreamWaitEvent(io.d2h, io.sweep_done[rs], 0));
+    if (flags & 1)
+        B200_CHECK_CUDA(cudaMemcpyAsync(io.resid_stage + rs, rdev, sizeof(double), cudaMemcpyDeviceToHost, io.d2h));
+    B200_CHECK_CUDA(cudaEventRecord(io.resid_copied[rs], io.d2h));
+    *ticket = io.seq++;
+    B2C_CATCH
+}
+
+// Block until call `ticket` of b2c_stencil_step_io has finished on the device and its residual
+// (local sum of squared updates of the last time step) is in host memory; returns it.
+B2C_EXPORT int b2c_stencil_io_wait(b2c_stencil* h, unsigned long long ticket, double* resid) {
+    B2C_TRY
+    B200_REQUIRE(h && h->p.io, ERR_ARG, "no pipelined step was issued");
+    IoState& io = *h->p.io;
+    B200_REQUIRE(ticket < io.seq && io.seq - ticket <= 2, ERR_ARG,
+                 "only the last two pipelined steps can be waited for");
+    B200_CHECK_CUDA(cudaEventSynchronize(io.resid_copied[ticket & 1]));
+    if (resid) *resid = io.resid_stage[ticket & 1];
     B2C_CATCH
 }
 

@@ -75,6 +75,14 @@ struct TsParams {
     // [cta][0] start, [1] end of the boundary segments, [2] end, [3] ns the producer spent
     // waiting for halo flags; nullptr = off
     unsigned long long* stamps;
+    // Tail work of the sweep, done by the LAST CTA to finish (ticket counter that wraps to 0, the
+    // single-launch reduction of mpicuda4.cu:157-185 in the reference): sum the per-CTA residual
+    // partials into *resid_out (resid != 0) and advance the device step counter by `bump`.
+    // tail_ticket == nullptr: neither (the host launches separate kernels for both).
+    unsigned* tail_ticket;
+    double* resid_out;
+    unsigned long long* ctr_w;
+    unsigned long long bump;
 };
 
 // Dynamic shared memory: nslots ring slots, then the output stage (kTsOutSlots rows of SWMAX
@@ -273,7 +281,13 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
 #pragma unroll
     for (int k = 0; k < 5; ++k) c[k] = __ldg(P.coef + k);
     const int c0 = CPT * tid;           // my first column inside the strip
-    double racc = 0.0;
+    // residual: NRA accumulators -- a single one made every output row end in a chain of CPT
+    // dependent DFMAs that two warps per scheduler could not hide (+6 % per sweep); one per column
+    // spills
+    constexpr int NRA = 3;
+    double racc[NRA];
+#pragma unroll
+    for (int q = 0; q < NRA; ++q) racc[q] = 0.0;
     int slot = 0;                       // mirrors the producer's ring position
     uint32_t phase = 0;
     int os = 0;                         // mirrors the store thread's output slot
@@ -394,7 +408,7 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
                 for (int q = 0; q < CPT; ++q)
                     if (c0 + q < sw) {
                         const double d0 = outv[q] - ctr[q];
-                        racc = fma(d0, d0, racc);
+                        racc[q % NRA] = fma(d0, d0, racc[q % NRA]);
                     }
             }
             if (ACT) {
@@ -487,14 +501,49 @@ stencil_tstrip_kernel(const __grid_constant__ TsParams SP) {
     if (SP.resid) {
         // deterministic per-CTA partial: lanes -> warps -> thread 0
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) racc += __shfl_xor_sync(0xffffffffu, racc, o);
-        if (lane == 0) red_smem[warp] = racc;
+        double rsum = 0.0;
+#pragma unroll
+        for (int q = 0; q < NRA; ++q) rsum += racc[q];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) rsum += __shfl_xor_sync(0xffffffffu, rsum, o);
+        if (lane == 0) red_smem[warp] = rsum;
         ptx::named_bar_sync(2, G::CONS);
         if (tid == 0) {
             double t = 0.0;
 #pragma unroll
             for (int w = 0; w < NWARPS; ++w) t += red_smem[w];
             P.resid_partials[blockIdx.x] = t;
+        }
+    }
+    if (SP.tail_ticket) {
+        static_assert(G::CONS == 256, "the tail reduction mirrors sum_partials_kernel<<<1, 256>>>");
+        __shared__ int is_last;
+        if (tid == 0) {
+            __threadfence();                      // my partial before my ticket
+            const unsigned last = gridDim.x - 1;
+            is_last = atomicInc(SP.tail_ticket, last) == last;
+        }
+        ptx::named_bar_sync(2, G::CONS);
+        if (is_last) {
+            // Every other CTA has taken its ticket, so its consumers are done, so its producer
+            // has read the step counter for the last time: the counter may move now.
+            __threadfence();
+            if (SP.resid) {
+                // same summation tree as sum_partials_kernel: the two paths agree bit for bit.
+                // The ring slots are idle by now (every load was consumed).
+                double* sh = reinterpret_cast<double*>(smem);
+                double a = 0.0;
+                for (int i = tid; i < (int)gridDim.x; i += G::CONS) a += __ldcg(P.resid_partials + i);
+                sh[tid] = a;
+                ptx::named_bar_sync(2, G::CONS);
+#pragma unroll 1
+                for (int o = G::CONS / 2; o > 0; o >>= 1) {
+                    if (tid < o) sh[tid] += sh[tid + o];
+                    ptx::named_bar_sync(2, G::CONS);
+                }
+                if (tid == 0) *SP.resid_out = sh[0];
+            }
+            if (tid == 0 && SP.bump) *SP.ctr_w += SP.bump;
         }
     }
 }

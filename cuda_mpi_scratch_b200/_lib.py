@@ -153,6 +153,8 @@ _proto("b2c_stencil_set_timeout_ms", [vp, u64])
 _proto("b2c_stencil_info", [vp, C.POINTER(StencilInfo)])
 _proto("b2c_stencil_step", [vp, i32, i32, vp])
 _proto("b2c_stencil_step_levels", [vp, i32, i32, vp])
+_proto("b2c_stencil_step_io", [vp, i32, i32, C.POINTER(C.c_double), i32, vp, C.POINTER(C.c_ulonglong)])
+_proto("b2c_stencil_io_wait", [vp, C.c_ulonglong, C.POINTER(C.c_double)])
 _proto("b2c_stencil_drain", [vp, vp])
 _proto("b2c_stencil_advance", [vp, C.c_longlong])
 _proto("b2c_stencil_exchange_push", [vp, vp])

@@ -236,6 +236,36 @@ class Stencil2D:
                     _lib.check(L.b2c_stencil_step_levels(self._h, rem, flags, st))
         self._time_steps += nsteps
 
+    def step_io(self, nsteps: int, coeffs: Sequence[float] | torch.Tensor | None = None,
+                residual: bool = True, drain: bool = True) -> int:
+        """Pipelined :meth:`step` for loops that hand in coefficients and read the residual
+        EVERY call: the host->device copy of ``coeffs`` (staged through pinned memory of the
+        plan) and the device->host copy of the residual run on the plan's own copy streams, next
+        to the kernels of the previous and the next call, and the current stream carries the
+        sweep kernels only.  Returns a ticket for :meth:`wait_io`; the results of the last two
+        calls are kept, so a loop stays one call ahead of the result it reads."""
+        flags = (1 if residual else 0) | (2 if drain else 0)
+        ticket = C.c_ulonglong(0)
+        if coeffs is None:
+            ptr, n = None, 0
+        else:
+            ct = coeffs if isinstance(coeffs, torch.Tensor) else torch.as_tensor(coeffs, dtype=torch.float64)
+            if ct.dtype != torch.float64 or ct.device.type != "cpu" or not ct.is_contiguous():
+                ct = ct.to(device="cpu", dtype=torch.float64).contiguous()
+            ptr, n = C.cast(ct.data_ptr(), C.POINTER(C.c_double)), ct.numel()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib.b2c_stencil_step_io(self._h, nsteps, flags, ptr, n,
+                                                    _stream_ptr(self.device), C.byref(ticket)))
+        self._time_steps += nsteps
+        return int(ticket.value)
+
+    def wait_io(self, ticket: int) -> float:
+        """Block until call ``ticket`` of :meth:`step_io` has run on the device; returns its local
+        sum of squared updates of the last time step (0.0 if no residual was asked for)."""
+        r = C.c_double(0.0)
+        _lib.check(_lib.lib.b2c_stencil_io_wait(self._h, int(ticket), C.byref(r)))
+        return float(r.value)
+
     def _sweeps(self, nsteps: int) -> int:
         """Kernel sweeps that :meth:`step` launches for ``nsteps`` time steps."""
         return -(-nsteps // self.temporal)

@@ -254,6 +254,15 @@ int b2c_stencil_step(b2c_stencil* s, int nsteps, int flags, void* stream);
 /* kind 2 (temporal blocking: radius-1 star, `radius` time levels per sweep): one sweep that
  * computes only `levels` (1..radius) levels -- the tail of a run that is not a multiple */
 int b2c_stencil_step_levels(b2c_stencil* s, int levels, int flags, void* stream);
+/* One call of a pipelined loop: `nsteps` time steps (any count) with this call's coefficients
+ * taken from host memory (NULL: unchanged) and its residual (flags bit0) returned to host
+ * memory.  Both copies run on copy streams of the plan, next to the kernels of the neighbouring
+ * calls; `stream` carries the kernels only.  *ticket names the call; b2c_stencil_io_wait blocks
+ * until that call has finished on the device and hands out its residual (local sum of squared
+ * updates).  The results of the last two calls are kept. */
+int b2c_stencil_step_io(b2c_stencil* s, int nsteps, int flags, const double* host_coef, int n,
+                        void* stream, unsigned long long* ticket);
+int b2c_stencil_io_wait(b2c_stencil* s, unsigned long long ticket, double* resid);
 /* after replaying a captured CUDA graph of `nsteps` steps: advance the host-side step count */
 int b2c_stencil_advance(b2c_stencil* s, long long nsteps);
 int b2c_stencil_drain(b2c_stencil* s, void* stream);

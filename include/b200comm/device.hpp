@@ -194,6 +194,24 @@ public:
         }
         steps_ += n;
     }
+    // Pipelined variant for loops that feed coefficients in and read the residual out EVERY call:
+    // the copies run on the plan's copy streams next to the neighbouring calls' kernels.  Returns
+    // a ticket for wait_io(); keep at most two calls in flight.
+    unsigned long long step_io(int n, const std::vector<double>* coeffs = nullptr, bool residual = true,
+                               bool drain = true) {
+        const int flags = (residual ? 1 : 0) | (drain ? 2 : 0);
+        unsigned long long ticket = 0;
+        B200_DEVICE_OK(b2c_stencil_step_io(h_, n, flags, coeffs ? coeffs->data() : nullptr,
+                                           coeffs ? (int)coeffs->size() : 0, stream_, &ticket));
+        steps_ += n;
+        return ticket;
+    }
+    // Blocks until that call has run; returns its LOCAL sum of squared updates.
+    double wait_io(unsigned long long ticket) {
+        double r = 0.0;
+        B200_DEVICE_OK(b2c_stencil_io_wait(h_, ticket, &r));
+        return r;
+    }
     void synchronize() { B200_DEVICE_OK(b2c_stream_synchronize(stream_)); }
     // Global L2 norm of the last update (after step(..., residual = true)); collective.
     double residual() {

@@ -219,6 +219,57 @@ def test_temporal_strip_kernel_is_bit_identical_to_single_steps(monkeypatch, dim
     assert torch.allclose(s.tile.cpu(), exp[ri][:, ci], rtol=1e-12, atol=1e-13)
 
 
+@pytest.mark.parametrize("T,algo,hw", [(1, "strip", (96, 600)), (3, "strip", (96, 1900)), (3, "tile", (96, 384)),
+                                       (2, "strip", (64, 3200))])
+def test_pipelined_step_io_equals_set_coeffs_step_residual(monkeypatch, T, algo, hw):
+    """``step_io`` (coefficients in and residual out on the plan's copy streams, one call kept in
+    flight) against the plain sequence set_coeffs / step(residual) / residual on a twin plan:
+    same field bits and the same residual for every call, with coefficients that change every
+    call and step counts that are not multiples of the levels per sweep."""
+    monkeypatch.setenv("B2C_TB_ALGO", algo)
+    glob = _rand_global(hw[0], hw[1], 3)
+
+    def make():
+        grp = Stencil2D.create_group(cms.LocalGroup(1), hw, 1, "star", dims=(1, 1), temporal=T)
+        s = grp.ranks[0]
+        s.fill(0.0, 0.0)
+        grp.scatter_global(glob)
+        grp.exchange()
+        return grp, s
+
+    ga, a = make()
+    gb, b = make()
+    counts = [T, T, 2 * T + 1, 1, T, 3 * T, T + 1 if T > 1 else 2]
+    coefs = [[0.1 + 0.01 * i, 0.2, 0.25 - 0.01 * i, 0.15, 0.3] for i in range(len(counts))]
+    want = []
+    for n, c in zip(counts, coefs):
+        b.set_coeffs(c)
+        b.step(n, residual=True)
+        buf = b.local_residual_async()
+        torch.cuda.synchronize()
+        want.append(float(buf.item()))
+    got, pend = [], None
+    for i, (n, c) in enumerate(zip(counts, coefs)):
+        cc = c if i % 2 else torch.tensor(c, dtype=torch.float64).pin_memory()
+        t = a.step_io(n, cc, residual=True, drain=(i == len(counts) - 1))
+        if pend is not None:
+            got.append(a.wait_io(pend))
+        pend = t
+    got.append(a.wait_io(pend))
+    a.check()
+    b.check()
+    assert got == want
+    assert a.steps_done == b.steps_done == sum(counts)
+    assert torch.equal(ga.gather_global(), gb.gather_global())
+    with pytest.raises(cms.CommError):
+        a.wait_io(0)                       # more than two calls back
+    # plain steps afterwards keep the coefficients of the last pipelined call
+    a.step(T)
+    b.step(T)
+    torch.cuda.synchronize()
+    assert torch.equal(ga.gather_global(), gb.gather_global())
+
+
 @pytest.mark.parametrize("T", [2, 3])
 def test_temporal_strip_kernel_graph_replay_and_odd_step_counts(monkeypatch, T):
     monkeypatch.setenv("B2C_TB_ALGO", "strip")
