@@ -82,6 +82,16 @@ def reference_arm(args) -> int:
     return 0
 
 
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL writes its
+    version line to stdout when NCCL_DEBUG is set on the box), so file descriptor 1 is pointed at
+    stderr for the duration of the run and the JSON line goes to the original stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(real, "w")
+
+
 def _stats(ms_list, steps):
     per = sorted(m / steps for m in ms_list)
     return {"median": statistics.median(per), "min": per[0], "max": per[-1], "batches": len(per)}
@@ -101,6 +111,7 @@ def main(argv=None) -> int:
     if not torch.cuda.is_available():
         print(json.dumps({"error": "no CUDA device"}))
         return 1
+    result_out = _claim_stdout()
     world = cms.init()
     n = world.size
     if n != args.gpus:
@@ -350,10 +361,11 @@ def main(argv=None) -> int:
                     "last_residual_sumsq": last_res[0]},
             "gpu_launches": launches,
             "launches_note": "kernels of ONE timed K-step batch, counted by the native plan: 1 fused "
-                             f"stencil+halo kernel per sweep ({T} time step(s) each), then 1 "
-                             "step-counter bump, 1 flag drain and 1 ghost-column unpack per batch",
+                             f"stencil+halo kernel per sweep ({T} time step(s) each; its last CTA "
+                             "advances the device step counter), then 1 flag drain and 1 "
+                             "ghost-column unpack per batch",
         }
-        print(json.dumps(out))
+        print(json.dumps(out), file=result_out, flush=True)
     world.barrier()
     for p in (st, st1, loc):
         if p is not None:

@@ -104,6 +104,22 @@ int main(int argc, char** argv) {
                       << " steps (" << temporal << " per sweep): " << (emax - bmin) / steps * 1e3 << " ms/step, "
                       << cells * steps / (emax - bmin) / 1e9 << " Gcell/s, residual " << res << std::endl;
 
+        // The same steps as a loop that hands in coefficients and reads the residual back EVERY
+        // call (step_io / wait_io: the copies run next to the neighbouring calls' kernels).
+        const int io_calls = 4, extra = io_calls * temporal;
+        double io_local = 0.0, io_sum = 0.0;
+        {
+            unsigned long long pend = 0;
+            for (int i = 0; i < io_calls; ++i) {
+                const unsigned long long t = st.step_io(temporal, &coef, /*residual=*/true, /*drain=*/i == io_calls - 1);
+                if (i) io_local = st.wait_io(pend);
+                pend = t;
+            }
+            io_local = st.wait_io(pend);
+            st.check();
+            cart.allreduce(&io_local, &io_sum, 1, dbl, Op::SUM);
+        }
+
         if ((long long)GH * GW <= (1 << 22)) {         // small enough to redo on the host
             st.download_core(tile.data());
             std::vector<double> all(me == 0 ? (size_t)n * tile.size() : 0);
@@ -114,6 +130,8 @@ int main(int argc, char** argv) {
                     for (int x = 0; x < GW; ++x) g[(size_t)y * GW + x] = init(y, x);
                 double sumsq = 0.0;
                 g = host_steps(std::move(g), GH, GW, warm + steps, coef.data(), &sumsq);
+                double sumsq_io = 0.0;
+                g = host_steps(std::move(g), GH, GW, extra, coef.data(), &sumsq_io);
                 double err = 0.0;
                 for (int r = 0; r < n; ++r) {
                     const std::vector<int> rc2 = cart.cart_coords(r);
@@ -122,8 +140,10 @@ int main(int argc, char** argv) {
                             err = std::max(err, std::fabs(all[(size_t)r * tile.size() + (size_t)y * side + x] -
                                                           g[(size_t)(rc2[0] * side + y) * GW + rc2[1] * side + x]));
                 }
-                const bool ok = err == 0.0 && std::fabs(res - std::sqrt(sumsq)) <= 1e-10 * std::sqrt(sumsq);
-                std::cout << "max |device - host| = " << err << ", host residual " << std::sqrt(sumsq) << "\n"
+                const bool ok = err == 0.0 && std::fabs(res - std::sqrt(sumsq)) <= 1e-10 * std::sqrt(sumsq) &&
+                                std::fabs(io_sum - sumsq_io) <= 1e-10 * sumsq_io;
+                std::cout << "max |device - host| = " << err << ", host residual " << std::sqrt(sumsq)
+                          << ", pipelined loop residual " << std::sqrt(io_sum) << " (host " << std::sqrt(sumsq_io) << ")\n"
                           << (ok ? "PASSED" : "FAILED") << std::endl;
                 rc = ok ? 0 : 1;
             }

@@ -86,6 +86,43 @@ def main():
     fails += 0 if ok else 1
     world.barrier()
     st.close()
+    # ---- pipelined loop: new coefficients in and the residual out EVERY call (step_io / wait_io),
+    # one call in flight, ranks free-running against each other
+    for tb in (1, 3):
+        th, tw = 512, 2048
+        g = torch.Generator().manual_seed(99)
+        glob = torch.rand(dims[0] * th, dims[1] * tw, dtype=torch.float64, generator=g)
+        st = Stencil2D.create(world, (th, tw), 1, "star", dims=dims, temporal=tb)
+        r, c = st.cart.coords(world.rank)
+        st.fill(0.0, 0.0)
+        st.core.copy_(glob[r * th:(r + 1) * th, c * tw:(c + 1) * tw])
+        torch.cuda.synchronize()
+        st.exchange()
+        counts = [tb, tb, 2 * tb + 1, tb, 1, 2 * tb]
+        coefs = [[0.1 + 0.01 * i, 0.2, 0.25 - 0.01 * i, 0.15, 0.3] for i in range(len(counts))]
+        got, pend = [], None
+        for i, (n, co) in enumerate(zip(counts, coefs)):
+            t = st.step_io(n, co, residual=True, drain=(i == len(counts) - 1))
+            if pend is not None:
+                got.append(st.wait_io(pend))
+            pend = t
+        got.append(st.wait_io(pend))
+        st.check()
+        exp, ok = glob, True
+        for n, co, loc in zip(counts, coefs, got):
+            for _ in range(n):
+                prev = exp
+                exp = reference_step(exp, co, 1, "star")
+            want = float(((exp - prev) ** 2).sum())
+            tot_res = world.allreduce_sum(loc)
+            ok = ok and abs(tot_res - want) <= 1e-10 * want
+        err = float((st.core.cpu() - exp[r * th:(r + 1) * th, c * tw:(c + 1) * tw]).abs().max())
+        ok = ok and err < 1e-12 and st.steps_done == sum(counts)
+        print(f"rank {world.rank}: pipelined step_io loop, temporal {tb}: err {err:.2e} "
+              f"{'OK' if ok else 'FAIL'}", flush=True)
+        fails += 0 if ok else 1
+        world.barrier()
+        st.close()
     tot = world.allreduce_sum(float(fails))
     if world.rank == 0:
         sys.stdout.write("MP_STENCIL_CHECK PASSED\n" if tot == 0 else f"MP_STENCIL_CHECK FAILED ({int(tot)})\n")
