@@ -35,6 +35,7 @@ def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--max-log2", type=int, default=28, help="largest allreduce payload, log2 bytes")
+    ap.add_argument("--min-log2", type=int, default=3, help="smallest allreduce payload, log2 bytes")
     ap.add_argument("--json", default="")
     a = ap.parse_args()
     world = cms.init()
@@ -78,7 +79,7 @@ def main() -> int:
 
     # ---------------- allreduce: sizes x algorithms ----------------
     for lg in [3, 10, 12, 14, 16, 18, 20, 22, 24, 26, 28, 30]:
-        if lg > a.max_log2:
+        if lg > a.max_log2 or lg < a.min_log2:
             continue
         n = (1 << lg) // 4
         if lg >= 30 and a.iters > 5:
