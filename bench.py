@@ -61,6 +61,7 @@ def parse_args(argv=None):
     ap.add_argument("--temporal", type=int, default=0, choices=[0, 1, 2, 3, 4],
                     help="time steps per kernel sweep: 2-4 = temporal blocking (radius 1 only), "
                          "1 = one step per sweep, 0 = 3 where possible")
+    ap.add_argument("--dims", default="", help="process grid PYxPX (default: balanced, like MPI_Dims_create)")
     ap.add_argument("--th", type=int, default=0, help="explicit per-GPU tile height (experiments)")
     ap.add_argument("--tw", type=int, default=0, help="explicit per-GPU tile width (experiments)")
     ap.add_argument("--min-seconds", type=float, default=2.0,
@@ -118,6 +119,15 @@ def main(argv=None) -> int:
         if world.rank == 0:
             print(f"warning: --gpus {args.gpus} but WORLD_SIZE={n}; using {n}", file=sys.stderr)
     dims = cms.dims_create(n, 2)
+    if args.scaling == "strong" and not args.dims and args.tile % n == 0 and args.tile // n >= 512:
+        # Fixed total work: row slabs keep every tile as wide as the grid.  The strip kernel wants
+        # wide tiles (11 full-width strips instead of 3, profiles/r2/tile_shapes_1gpu.txt) and the
+        # whole halo is then contiguous rows; the balanced 2 x 4 grid is --dims 2x4.
+        dims = (n, 1)
+    if args.dims:
+        dims = tuple(int(v) for v in args.dims.lower().split("x"))
+        if len(dims) != 2 or dims[0] * dims[1] != n:
+            raise SystemExit(f"--dims {args.dims} does not describe {n} ranks")
     if args.scaling == "weak":
         th = tw = args.tile
     else:  # strong: total work fixed at tile^2, split over the grid
