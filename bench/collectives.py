@@ -36,6 +36,8 @@ def main() -> int:
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--max-log2", type=int, default=28, help="largest allreduce payload, log2 bytes")
     ap.add_argument("--min-log2", type=int, default=3, help="smallest allreduce payload, log2 bytes")
+    ap.add_argument("--sweep-moves", action="store_true",
+                    help="also sweep bcast and allgather over message sizes (8 B .. the workspace)")
     ap.add_argument("--json", default="")
     a = ap.parse_args()
     world = cms.init()
@@ -166,6 +168,73 @@ def main() -> int:
     rows.append(with_clocks(rec))
     if rank == 0:
         print(rec, flush=True)
+
+    if a.sweep_moves:
+        # bcast (multimem.st fan-out through the switch when there is a multicast mapping) and
+        # allgather (every rank stores its block into every peer) over message sizes, against
+        # ncclBroadcast / ncclAllGather (all_gather_into_tensor)
+        it0 = a.iters
+        for lg in [3, 4, 10, 14, 18, 22, 24, 26, 28]:
+            if (1 << lg) > max_bytes:
+                continue
+            a.iters = it0 if lg < 26 else min(it0, 10)
+            nb = 1 << lg
+            t = torch.full((max(nb // 4, 2),), float(rank), dtype=torch.float32, device=device)
+            root = (lg // 2) % P
+            coll.bcast(t, root=root)
+            coll.check()
+            ok = bool((t == float(root)).all())
+            fails += 0 if ok else 1
+            rec = {"op": "bcast", "bytes": t.numel() * 4, "ok": ok,
+                   "ours_us": round(timed(lambda: coll.bcast(t, root=0)), 2),
+                   "nccl_us": round(timed(lambda: dist.broadcast(t, 0, group=pg)), 2),
+                   "multicast_store": bool(coll.multicast)}
+            if symm is not None and (t.numel() * 4) % 16 == 0:
+                # the same on a symmetric tensor: one multicast store pass, no staging
+                sl = symm[:t.numel()]
+                sl.fill_(float(rank))
+                torch.cuda.synchronize(dev); world.barrier()
+                coll.bcast_symmetric(sl, root=root)
+                coll.check()
+                ok = bool((sl == float(root)).all())
+                fails += 0 if ok else 1
+                rec["symmetric_us"] = round(timed(lambda: coll.bcast_symmetric(sl, root=0)), 2)
+                rec["symmetric_ok"] = ok
+            rows.append(with_clocks(rec))
+            if rank == 0:
+                print(rec, flush=True)
+            del t
+        for lg in [3, 4, 10, 14, 18, 22, 25]:
+            nb = 1 << lg
+            if nb * P > max_bytes:
+                continue
+            a.iters = it0 if lg < 22 else min(it0, 10)
+            sblk = torch.full((max(nb // 4, 2),), float(rank + 1), dtype=torch.float32, device=device)
+            rbuf = torch.zeros(P * sblk.numel(), dtype=torch.float32, device=device)
+            coll.allgather(sblk, rbuf)
+            coll.check()
+            want_ag = torch.arange(1, P + 1, dtype=torch.float32, device=device).repeat_interleave(sblk.numel())
+            ok = bool(torch.equal(rbuf, want_ag))
+            fails += 0 if ok else 1
+            rec = {"op": "allgather", "bytes_per_rank": sblk.numel() * 4, "ok": ok,
+                   "ours_us": round(timed(lambda: coll.allgather(sblk, rbuf)), 2),
+                   "nccl_us": round(timed(lambda: dist.all_gather_into_tensor(rbuf, sblk, group=pg)), 2)}
+            if symm is not None and (sblk.numel() * 4) % 16 == 0:
+                sl = symm[:P * sblk.numel()]
+                sl.zero_()
+                sl[rank * sblk.numel():(rank + 1) * sblk.numel()].copy_(sblk)
+                torch.cuda.synchronize(dev); world.barrier()
+                coll.allgather_symmetric(sl)
+                coll.check()
+                ok = bool(torch.equal(sl, want_ag))
+                fails += 0 if ok else 1
+                rec["symmetric_us"] = round(timed(lambda: coll.allgather_symmetric(sl)), 2)
+                rec["symmetric_ok"] = ok
+            rows.append(with_clocks(rec))
+            if rank == 0:
+                print(rec, flush=True)
+            del sblk, rbuf, want_ag
+        a.iters = it0
 
     g_recv = torch.zeros(P * 256, dtype=torch.float32, device=device) if rank == 0 else None
     g_send = torch.full((256,), float(rank + 1), dtype=torch.float32, device=device)

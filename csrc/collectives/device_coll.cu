@@ -382,6 +382,44 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_inplace_kernel(const 
     }
 }
 
+// bcast / allgather in place on a SYMMETRIC tensor: this rank's byte range [lo, hi) of the tensor
+// (bcast: the whole tensor on the root, nothing elsewhere; allgather: block `rank`) is read from
+// the local copy and stored ONCE to the multicast address -- the switch delivers it to every
+// rank's copy.  One pass over the data, no staging.  ready-barrier (every rank has reached the
+// operation, so its copy may be overwritten), stores, done-barrier (every range has landed here).
+__global__ void __launch_bounds__(kThreads) spread_inplace_kernel(const __grid_constant__ Ws w,
+                                                                  unsigned char* mc_data,
+                                                                  const unsigned char* local_data,
+                                                                  size_t lo, size_t hi, uint64_t epoch) {
+    __shared__ bool last;
+    if (blockIdx.x == 0) signal_all(w, kOffReady, epoch);
+    if (!wait_all(w, kOffReady, epoch)) return;
+    const int64_t v0 = (int64_t)(lo / 16), v1 = (int64_t)((hi + 15) / 16);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t v = v0 + tid; v < v1; v += nthr * kVecUnroll) {
+        int4 acc[kVecUnroll];
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v + k * nthr < v1) acc[k] = __ldcg(reinterpret_cast<const int4*>(local_data) + v + k * nthr);
+#pragma unroll
+        for (int k = 0; k < kVecUnroll; ++k)
+            if (v + k * nthr < v1) mm_st_v4(mc_data + (v + k * nthr) * 16, acc[k]);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::fence_acq_rel_sys();
+        unsigned int* cnt = reinterpret_cast<unsigned int*>(w.peer[w.rank] + kOffCounter);
+        last = atomicInc(cnt, gridDim.x - 1) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last) signal_all(w, kOffDone, epoch);
+    if (!wait_all(w, kOffDone, epoch)) return;
+    if (gridDim.x == 1) {
+        signal_all(w, kOffConsumed, epoch);
+        if (epoch > 1) wait_all(w, kOffConsumed, epoch - 1);
+    }
+}
+
 // bcast through the switch: the root stores its buffer ONCE to the multicast address of
 // OUT[parity]; every rank (the root included) then copies out of its own staging.
 __global__ void __launch_bounds__(kThreads) push_mc_kernel(const __grid_constant__ Ws w,
@@ -647,6 +685,34 @@ B2C_EXPORT int b2c_coll_allreduce_symmetric(b2c_coll* h, void* mc_data, int64_t 
     }
     B200_CHECK_LAUNCH();
     if (grid > 1) {             // (a single CTA does the consumed-epoch exchange itself)
+        tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
+        B200_CHECK_LAUNCH();
+    }
+    B2C_CATCH
+}
+
+// In place on a symmetric tensor (multicast address `mc_data`, this rank's own mapping
+// `local_data`): store my byte range [lo, hi) into every rank's copy through the switch.
+// bcast: lo = 0, hi = bytes on the root and lo = hi elsewhere; allgather: block `rank`.
+// Ranges are 16-byte granular (symmetric blocks are 4 KiB granular, so rounding hi up is safe
+// only for the LAST range: callers pass block sizes that are multiples of 16).
+B2C_EXPORT int b2c_coll_spread_symmetric(b2c_coll* h, void* mc_data, const void* local_data, size_t lo,
+                                         size_t hi, void* stream) {
+    B2C_TRY
+    trace::Scope ts("coll_spread_symmetric(enqueue)", "device", -1, -3, -1, (int64_t)(hi - lo));
+    B200_REQUIRE(h && mc_data && local_data && lo <= hi, ERR_ARG, "bad argument");
+    B200_REQUIRE((((uintptr_t)mc_data | (uintptr_t)local_data | lo) & 15) == 0, ERR_BUFFER,
+                 "symmetric tensors and block offsets must be 16-byte aligned");
+    Plan& p = h->p;
+    cudaStream_t st = (cudaStream_t)stream;
+    p.epoch += 1;
+    const int64_t nvec = (int64_t)((hi - lo + 15) / 16);
+    // the whole grid waits on flags: keep it co-resident
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + kThreads * kVecUnroll - 1) / (kThreads * kVecUnroll), p.sms * 2));
+    spread_inplace_kernel<<<grid, kThreads, 0, st>>>(p.ws, static_cast<unsigned char*>(mc_data),
+                                                     static_cast<const unsigned char*>(local_data), lo, hi, p.epoch);
+    B200_CHECK_LAUNCH();
+    if (grid > 1) {
         tail_kernel<<<1, 64, 0, st>>>(p.ws, p.epoch);
         B200_CHECK_LAUNCH();
     }

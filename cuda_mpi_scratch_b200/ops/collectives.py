@@ -29,6 +29,7 @@ _lib._proto("b2c_coll_create", [C.POINTER(_vp), _i32, _i32, C.POINTER(_vp), C.c_
 _lib._proto("b2c_coll_destroy", [_vp])
 _lib._proto("b2c_coll_set_multicast", [_vp, _vp, _i32])
 _lib._proto("b2c_coll_allreduce_symmetric", [_vp, _vp, _i64, _i32, _vp])
+_lib._proto("b2c_coll_spread_symmetric", [_vp, _vp, _vp, C.c_size_t, C.c_size_t, _vp])
 _lib._proto("b2c_coll_allreduce", [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp])
 _lib._proto("b2c_coll_move", [_vp, _i32, _vp, _vp, C.c_size_t, _i32, _i32, _vp])
 _lib._proto("b2c_coll_barrier", [_vp, _i32, _vp])
@@ -134,6 +135,36 @@ class DeviceCollectives:
             _lib.check(_L.b2c_coll_allreduce_symmetric(self._h, C.c_void_p(sym.mc_ptr), t.numel(), _DT[t.dtype],
                                                        _stream(self.device)))
         self.kernel_launches += 2
+        return t
+
+    def _spread_symmetric(self, t: torch.Tensor, lo: int, hi: int) -> None:
+        sym = getattr(self, "_symm", {}).get(t.data_ptr())
+        if sym is None or not t.is_contiguous():
+            raise ValueError("needs a (slice from the start of a) tensor made by symmetric_empty")
+        with torch.cuda.device(self.device):
+            _lib.check(_L.b2c_coll_spread_symmetric(self._h, C.c_void_p(sym.mc_ptr), C.c_void_p(t.data_ptr()),
+                                                    lo, hi, _stream(self.device)))
+        self.kernel_launches += 2
+
+    def bcast_symmetric(self, t: torch.Tensor, root: int = 0) -> torch.Tensor:
+        """``MPI_Bcast`` in place on a tensor from :meth:`symmetric_empty`: the root stores it ONCE
+        to the multicast address and the switch writes every rank's copy -- one pass, no staging
+        (``mpicuda2.cu:154`` broadcasts a host scalar)."""
+        nb = t.numel() * t.element_size()
+        if nb % 16:
+            raise ValueError("bcast_symmetric moves whole 16-byte vectors: pad the tensor")
+        self._spread_symmetric(t, 0, nb if self.rank == root else 0)
+        return t
+
+    def allgather_symmetric(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place allgather (``MPI_IN_PLACE``) on a tensor from :meth:`symmetric_empty` of
+        ``nranks`` equal blocks: block ``rank`` holds this rank's contribution on entry, every block
+        is filled on return.  Each rank stores its block once through the switch."""
+        nb = t.numel() * t.element_size()
+        if nb % self.nranks or (nb // self.nranks) % 16:
+            raise ValueError("the tensor must split into nranks blocks of a multiple of 16 bytes")
+        blk = nb // self.nranks
+        self._spread_symmetric(t, self.rank * blk, (self.rank + 1) * blk)
         return t
 
     def reduce(self, t: torch.Tensor, root: int, op: str = "sum", out: torch.Tensor | None = None,

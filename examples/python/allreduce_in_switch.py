@@ -42,6 +42,22 @@ def main() -> int:
         world.barrier()
         coll.allreduce_symmetric(s)                           # zero-copy, reduced and fanned out by the switch
         ok = ok and bool((s == P * (P + 1) / 2).all())
+        # the other two collectives on the same tensor, in place: one multicast store pass each
+        blk = s.numel() // P
+        s.zero_()
+        s[rank * blk:(rank + 1) * blk] = float(rank + 1)
+        torch.cuda.synchronize(dev)
+        world.barrier()
+        coll.allgather_symmetric(s)                           # block r now holds r + 1 on every rank
+        want = torch.arange(1, P + 1, dtype=torch.float32, device=device).repeat_interleave(blk)
+        ok = ok and bool(torch.equal(s, want))
+        coll.barrier()                                        # everybody has checked before the tensor changes
+        torch.cuda.synchronize(dev)
+        world.barrier()
+        if rank == P - 1:
+            s.fill_(42.0)
+        coll.bcast_symmetric(s, root=P - 1)
+        ok = ok and bool((s == 42.0).all())
     r = torch.full((1024,), 1.0, dtype=torch.float64, device=device)
     coll.reduce(r, root=0)
     if rank == 0:

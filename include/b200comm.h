@@ -329,6 +329,11 @@ int b2c_coll_set_multicast(b2c_coll* c, void* mc_base, int mc_bcast);
 /* In-place SUM allreduce of a tensor that lives in a multicast arena of the symmetric heap
  * (`mc_data` = its multicast address): no staging copies, reduction and fan-out by the switch. */
 int b2c_coll_allreduce_symmetric(b2c_coll* c, void* mc_data, int64_t count, int dtype, void* stream);
+/* bcast / allgather in place on such a tensor: this rank's byte range [lo, hi) of it (`local_data`
+ * = this rank's own address of the tensor) is stored once to the multicast address and lands in
+ * every rank's copy.  bcast: [0, bytes) on the root, lo == hi elsewhere; allgather: block `rank`. */
+int b2c_coll_spread_symmetric(b2c_coll* c, void* mc_data, const void* local_data, size_t lo, size_t hi,
+                              void* stream);
 int b2c_coll_allreduce(b2c_coll* c, const void* in, void* out, int64_t count, int dtype, int op,
                        int root /* <0: allreduce */, int algo, int phases, void* stream);
 int b2c_coll_move(b2c_coll* c, int kind, const void* sendbuf, void* recvbuf, size_t block_bytes,
