@@ -46,6 +46,7 @@ dump allreduce_nvls_f32         'allreduce_nvls_kernelIfE'
 dump allreduce_nvls_inplace_f32 'allreduce_nvls_inplace_kernelIfE'
 dump coll_push                  'coll11push_kernel'
 dump coll_push_multicast        'push_mc_kernel'
+dump coll_spread_inplace        'spread_inplace_kernel'
 dump coll_pull_local            'pull_local_kernel'
 dump coll_barrier               'coll14barrier_kernel'
 dump coll_tail                  'coll11tail_kernel'
