@@ -95,6 +95,7 @@ class Stencil2D:
         self._coef_pinned = pin(torch.empty(2, 128, dtype=torch.float64))
         self._resid_pinned = pin(torch.zeros(2, dtype=torch.float64))
         self._coef_slot = 0
+        self._coeffs: list[float] | None = None     # last coefficients handed in (None: the plan's default)
         self._graph_launches = 0
         self._time_steps = 0
 
@@ -193,6 +194,7 @@ class Stencil2D:
         stage = self._coef_pinned[self._coef_slot]
         self._coef_slot ^= 1
         stage[:n] = torch.as_tensor(coeffs, dtype=torch.float64)
+        self._coeffs = stage[:n].tolist()
         ptr = C.cast(stage.data_ptr(), C.POINTER(C.c_double))
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_set_coef(self._h, ptr, n, _stream_ptr(self.device)))
@@ -253,6 +255,7 @@ class Stencil2D:
             if ct.dtype != torch.float64 or ct.device.type != "cpu" or not ct.is_contiguous():
                 ct = ct.to(device="cpu", dtype=torch.float64).contiguous()
             ptr, n = C.cast(ct.data_ptr(), C.POINTER(C.c_double)), ct.numel()
+            self._coeffs = ct.tolist()
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib.b2c_stencil_step_io(self._h, nsteps, flags, ptr, n,
                                                     _stream_ptr(self.device), C.byref(ticket)))
@@ -381,13 +384,14 @@ class Stencil2D:
 
     # ------------------------------------------------------------ checkpoint / resume
     def save_checkpoint(self, path: str) -> None:
-        """Write this rank's state (core cells, ghost cells, step count, geometry) to ``path``.
+        """Write this rank's state (core cells, ghost cells, coefficients, step count, geometry) to ``path``.
         The reference has no checkpointing, only the per-rank text dump
         (``mpi-2d-stencil-subarray-cuda.cu:114-119,164-176``); this is the binary form of it."""
         torch.cuda.current_stream(self.device).synchronize()
         torch.save({"tile": self.tile.cpu(), "steps_done": self.steps_done, "temporal": self.temporal,
                     "rank": self.rank, "dims": self.cart.dims, "periods": self.cart.periods,
-                    "tile_hw": (self.H, self.W), "radius": self.radius, "kind": self.kind}, path)
+                    "tile_hw": (self.H, self.W), "radius": self.radius, "kind": self.kind,
+                    "coeffs": self._coeffs}, path)
 
     def load_checkpoint(self, path: str) -> int:
         """Restore the state saved by :meth:`save_checkpoint` into the CURRENT buffer (core and
@@ -398,6 +402,8 @@ class Stencil2D:
                 or ck["rank"] != self.rank or ck.get("temporal", 1) != self.temporal:
             raise ValueError("checkpoint does not match this plan (tile size, radius or rank)")
         self.tile.copy_(ck["tile"].to(self.tile.device))
+        if ck.get("coeffs") is not None:          # coefficients are part of the state
+            self.set_coeffs(ck["coeffs"])
         torch.cuda.current_stream(self.device).synchronize()
         return int(ck["steps_done"])
 

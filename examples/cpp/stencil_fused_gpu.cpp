@@ -10,6 +10,7 @@
 // redo on the host -- a comparison of every rank's tile with a host computation of the GLOBAL grid.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <iostream>
 #include <vector>
@@ -148,6 +149,32 @@ int main(int argc, char** argv) {
                 rc = ok ? 0 : 1;
             }
             world.bcast(&rc, 1, Datatype::basic(Basic::INT32), 0);
+
+            // Checkpoint / resume: a fresh plan restored from this rank's file continues with
+            // the same bits as the plan that wrote it.
+            const std::string ck = "/tmp/stencil_fused_gpu_" + std::to_string((long long)getpid()) + "_" +
+                                   std::to_string(me) + ".ckpt";
+            st.save_checkpoint(ck);
+            st.step(2 * temporal + 1);
+            st.synchronize();
+            std::vector<double> cont(tile.size()), again(tile.size());
+            st.download_core(cont.data());
+            {
+                FusedStencil st2(cart, side, side, 1, FusedStencil::Star, temporal);
+                st2.fill(0.0, 0.0);
+                const long long at = st2.load_checkpoint(ck);
+                st2.exchange();
+                st2.step(2 * temporal + 1);
+                st2.synchronize();
+                st2.check();
+                st2.download_core(again.data());
+                int same = (at == warm + steps + extra && cont == again) ? 1 : 0, all_same = 0;
+                cart.allreduce(&same, &all_same, 1, Datatype::basic(Basic::INT32), Op::MIN);
+                if (me == 0) std::cout << "checkpoint at step " << at << ", resumed run "
+                                       << (all_same ? "bit-identical" : "DIFFERS") << std::endl;
+                if (!all_same) rc = 1;
+            }
+            std::remove(ck.c_str());
         }
     }   // the plan and its symmetric block are released here (collective)
     finalize(world);

@@ -13,6 +13,7 @@
 #include <unistd.h>
 
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -162,6 +163,60 @@ public:
         for (int y = 0; y < H_ + 2 * g; ++y)
             std::memcpy(host + (size_t)y * tw, padded.data() + (size_t)y * lay_.pitch + lay_.lead - g, sizeof(double) * tw);
     }
+    // Inverse of download_tile: core AND ghost ring of the current buffer from a host array.
+    void upload_tile(const double* host) {
+        const b2c_stencil_info_t inf = info();
+        const int g = lay_.ghost, tw = W_ + 2 * g;
+        std::vector<double> padded((size_t)lay_.rows * lay_.pitch);
+        const size_t nbytes = padded.size() * sizeof(double);
+        B200_DEVICE_OK(b2c_memcpy_async(padded.data(), inf.buf[inf.cur], nbytes, 2, stream_));
+        B200_DEVICE_OK(b2c_stream_synchronize(stream_));
+        for (int y = 0; y < H_ + 2 * g; ++y)
+            std::memcpy(padded.data() + (size_t)y * lay_.pitch + lay_.lead - g, host + (size_t)y * tw, sizeof(double) * tw);
+        B200_DEVICE_OK(b2c_memcpy_async(inf.buf[inf.cur], padded.data(), nbytes, 1, stream_));
+        B200_DEVICE_OK(b2c_stream_synchronize(stream_));
+    }
+    // Checkpoint / resume of this rank's state: geometry, step count, coefficients, the tile with
+    // its ghost ring (one binary file per rank).  The reference only has the per-rank text dump
+    // (stencil2d/mpi-2d-stencil-subarray-cuda.cu:114-119,164-176).  After load_checkpoint() on a
+    // fresh plan of the same geometry call exchange() on all ranks; the continuation is
+    // bit-identical.  Returns the step count of the checkpoint.
+    void save_checkpoint(const std::string& path) {
+        const int g = lay_.ghost;
+        std::vector<double> tile((size_t)(H_ + 2 * g) * (W_ + 2 * g));
+        download_tile(tile.data());
+        const long long hdr[8] = {kCheckpointMagic, H_, W_, radius_, temporal_, steps_, (long long)coef_.size(),
+                                  (long long)cart_.rank()};
+        std::FILE* f = std::fopen(path.c_str(), "wb");
+        bool ok = f != nullptr;
+        ok = ok && std::fwrite(hdr, sizeof(hdr), 1, f) == 1;
+        ok = ok && (coef_.empty() || std::fwrite(coef_.data(), sizeof(double), coef_.size(), f) == coef_.size());
+        ok = ok && std::fwrite(tile.data(), sizeof(double), tile.size(), f) == tile.size();
+        if (f) ok = (std::fclose(f) == 0) && ok;
+        if (!ok) ::b200::fail_comm(ERR_STATE, "cannot write checkpoint " + path, __FILE__, __LINE__);
+    }
+    long long load_checkpoint(const std::string& path) {
+        std::FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) ::b200::fail_comm(ERR_STATE, "cannot open checkpoint " + path, __FILE__, __LINE__);
+        long long hdr[8] = {0};
+        bool ok = std::fread(hdr, sizeof(hdr), 1, f) == 1;
+        if (ok && (hdr[0] != kCheckpointMagic || hdr[1] != H_ || hdr[2] != W_ || hdr[3] != radius_ ||
+                   hdr[4] != temporal_ || hdr[7] != cart_.rank())) {
+            std::fclose(f);
+            ::b200::fail_comm(ERR_ARG, "checkpoint does not match this plan (tile size, radius, levels or rank)",
+                              __FILE__, __LINE__);
+        }
+        std::vector<double> c((size_t)(ok ? hdr[6] : 0));
+        ok = ok && (c.empty() || std::fread(c.data(), sizeof(double), c.size(), f) == c.size());
+        const int g = lay_.ghost;
+        std::vector<double> tile((size_t)(H_ + 2 * g) * (W_ + 2 * g));
+        ok = ok && std::fread(tile.data(), sizeof(double), tile.size(), f) == tile.size();
+        std::fclose(f);
+        if (!ok) ::b200::fail_comm(ERR_STATE, "short read from checkpoint " + path, __FILE__, __LINE__);
+        if (!c.empty()) set_coeffs(c);
+        upload_tile(tile.data());
+        return hdr[5];
+    }
     void set_coeffs(const std::vector<double>& c) {
         coef_ = c;   // keeps the host copy alive until the asynchronous copy has been consumed
         B200_DEVICE_OK(b2c_stencil_set_coef(h_, coef_.data(), (int)coef_.size(), stream_));
@@ -252,6 +307,7 @@ private:
         }
     }
 
+    static constexpr long long kCheckpointMagic = 0x6232635f636b7074ll;   // "b2c_ckpt"
     comm::Comm cart_;
     int H_, W_, radius_, temporal_;
     void* stream_;

@@ -130,9 +130,11 @@ def test_gpu_fused_stencil_driver_from_cpp(tmp_path, temporal, steps):
     exe = _build("stencil_fused_gpu", tmp_path)
     p = _launch(1, exe, 256, steps, temporal)
     assert p.returncode == 0 and "PASSED" in p.stdout, p.stdout + p.stderr
+    assert "resumed run bit-identical" in p.stdout, p.stdout     # FusedStencil::save/load_checkpoint
     if torch.cuda.device_count() >= 2:      # one rank per GPU only
         p = _launch(2, exe, 256, steps, temporal)
         assert p.returncode == 0 and "PASSED" in p.stdout, p.stdout + p.stderr
+        assert "resumed run bit-identical" in p.stdout, p.stdout
 
 
 def test_mpi_shim_close_relatives(tmp_path):

@@ -386,7 +386,8 @@ def test_missing_neighbour_times_out_instead_of_hanging():
 
 def test_checkpoint_resume_continues_bit_identically(tmp_path):
     dims, hw = (2, 2), (64, 256)
-    grp, glob = _run_group(dims, hw, 1, "star", 3)
+    # non-default coefficients: they are part of the saved state
+    grp, glob = _run_group(dims, hw, 1, "star", 3, coeffs=[0.1, 0.2, 0.25, 0.15, 0.3])
     for s in grp.ranks:
         s.save_checkpoint(str(tmp_path / f"ck{s.rank}.pt"))
     grp.step(4)
