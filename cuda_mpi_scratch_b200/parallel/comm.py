@@ -116,10 +116,14 @@ def _bufinfo(buf, count=None, datatype: Datatype | None = None):
     dt = datatype
     nbytes = None
     if type(buf) is _np.ndarray:             # fast path: the common case of the host API
+        try:                                 # 0.7 us; __array_interface__ builds a dict (2.3 us)
+            addr = C.addressof(C.c_char.from_buffer(buf))
+        except (TypeError, ValueError):      # read-only, empty or strided array
+            addr = buf.__array_interface__["data"][0]
         if dt is None:
             dt = _basic_for(buf.dtype)
-            return buf.__array_interface__["data"][0], (buf.nbytes // max(dt.size, 1)) if count is None else count, dt, buf
-        return buf.__array_interface__["data"][0], 1 if count is None else count, dt, buf
+            return addr, (buf.nbytes // max(dt.size, 1)) if count is None else count, dt, buf
+        return addr, 1 if count is None else count, dt, buf
     if buf is None:
         return None, 0 if count is None else count, dt or _basic_for("byte"), None
     if isinstance(buf, int):
