@@ -32,3 +32,17 @@ def test_without_a_gpu_the_bench_fails_loudly():
                        timeout=300)
     assert p.returncode != 0
     assert "no CUDA device" in p.stdout
+
+
+def test_stdout_carries_only_the_json_line():
+    """bench.py points file descriptor 1 at stderr for the run (NCCL prints its version line to
+    stdout on some boxes) and writes the result to the original stdout."""
+    code = ("import os, sys; sys.path.insert(0, %r); import bench\n"
+            "out = bench._claim_stdout()\n"
+            "print('python noise')\n"
+            "os.write(1, b'library noise\\n')\n"
+            "print('{\"ok\": 1}', file=out, flush=True)\n" % ROOT)
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0
+    assert p.stdout == '{"ok": 1}\n'
+    assert "python noise" in p.stderr and "library noise" in p.stderr
