@@ -391,3 +391,76 @@ def test_rooted_reduce_without_acknowledgements_is_broken():
         except Violation:
             found += 1
     assert found > 0
+
+
+# ------------------------------------------------------------------------------------------------
+# Tail of a sweep inside the temporal strip kernel (csrc/stencil/stencil_tstrip_kernel.cuh, end of
+# the consumer path): every CTA writes its residual partial, fences, takes a ticket from a counter
+# that wraps at the grid size; the CTA that draws the last ticket sums ALL partials and advances the
+# device step counter.  The producers of all CTAs read that step counter during the sweep (epoch of
+# the halo flags), a consumer can only finish after its producer's last load.  Sweeps follow each
+# other in stream order (a new grid starts when the old one has ended).
+class SweepTailSim:
+    def __init__(self, ncta, nreads, sweeps, rng, ticket_before_partial=False, no_wrap=False):
+        self.G, self.R, self.S, self.rng = ncta, nreads, sweeps, rng
+        # consumer program of every CTA ("tail" is skipped by all but the drawer of the last ticket)
+        self.program = ["ticket", "tail", "partial"] if ticket_before_partial else ["partial", "ticket", "tail"]
+        self.no_wrap = no_wrap
+        self.ctr = 0                    # device step counter
+        self.ticket = 0
+        self.partials = [None] * ncta   # (sweep, value)
+
+    def run(self):
+        for sweep in range(self.S):
+            start_ctr = self.ctr
+            prod = [0] * self.G          # counter reads done by the producer of each CTA
+            pc = [0] * self.G            # position of each consumer in self.program
+            last = [False] * self.G
+            result = None
+            while any(p < self.R for p in prod) or any(c < len(self.program) for c in pc):
+                ready = [("p", i) for i in range(self.G) if prod[i] < self.R]
+                # a consumer reaches the end of its rows only after its producer issued every load
+                ready += [("c", i) for i in range(self.G) if pc[i] < len(self.program) and prod[i] == self.R]
+                kind, i = self.rng.choice(ready)
+                if kind == "p":
+                    if self.ctr != start_ctr:
+                        raise Violation(f"tail: producer of CTA {i} read the step counter after the bump")
+                    prod[i] += 1
+                    continue
+                op = self.program[pc[i]]
+                pc[i] += 1
+                if op == "partial":
+                    self.partials[i] = (sweep, i + 1)
+                elif op == "ticket":
+                    t = self.ticket
+                    self.ticket = 0 if (t + 1 == self.G and not self.no_wrap) else t + 1
+                    last[i] = t == self.G - 1
+                elif last[i]:            # "tail": sum every partial, advance the counter
+                    for j in range(self.G):
+                        if self.partials[j] is None or self.partials[j][0] != sweep:
+                            raise Violation(f"tail: sweep {sweep} summed a stale partial of CTA {j}")
+                    result = sum(v for _, v in self.partials)
+                    self.ctr += 1
+            if result is None:
+                raise Violation(f"tail: nobody drew the last ticket in sweep {sweep}")
+            if result != self.G * (self.G + 1) // 2:
+                raise Violation("tail: wrong sum")
+        if self.ctr != self.S:
+            raise Violation("tail: step counter")
+
+
+@pytest.mark.parametrize("ncta", [1, 2, 5, 16])
+def test_sweep_tail_last_cta_sums_and_bumps_safely(ncta):
+    for seed in range(100):
+        SweepTailSim(ncta, nreads=3, sweeps=4, rng=random.Random(seed)).run()
+
+
+@pytest.mark.parametrize("bug", ["ticket_before_partial", "no_wrap"])
+def test_sweep_tail_checker_finds_broken_variants(bug):
+    found = 0
+    for seed in range(200):
+        try:
+            SweepTailSim(5, nreads=2, sweeps=3, rng=random.Random(seed), **{bug: True}).run()
+        except Violation:
+            found += 1
+    assert found > 0
